@@ -1,0 +1,67 @@
+"""ctypes binding of libtcwarp.so (include/tcwarp.h).  No fallback: a missing library is an error."""
+from __future__ import annotations
+
+import ctypes
+import os
+from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_longlong, c_size_t, c_void_p
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(HERE, "libtcwarp.so")
+
+# flags (include/tcwarp.h)
+TCW_PER_UNIT_MAX = 1
+TCW_DETERMINISTIC = 2
+TCW_CLEAN = 4
+TCW_IS_IMAGE = 8
+
+# every symbol include/tcwarp.h declares: name -> (restype, argtypes)
+_FP, _IP, _VP = c_void_p, c_void_p, c_void_p      # device/host pointers are passed as raw addresses
+SIGNATURES = {
+    "tcw_create": (c_int, [c_int, POINTER(c_void_p)]),
+    "tcw_destroy": (None, [c_void_p]),
+    "tcw_version": (c_int, []),
+    "tcw_last_error": (c_char_p, []),
+    "tcw_launch_count": (c_longlong, [c_void_p]),
+    "tcw_workspace_bytes": (c_int, [c_void_p, c_int, c_int, c_int, c_int, POINTER(c_size_t)]),
+    "tcw_forward_warp": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int,
+                                 _VP, _VP, _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
+    "tcw_forward_warp_host": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int,
+                                      _VP, _VP, _FP, _FP, POINTER(c_int)]),
+    "tcw_project": (c_int, [c_void_p, _FP, _IP, _FP, c_int, c_int, c_int, c_int, _FP, c_void_p]),
+    "tcw_splat": (c_int, [c_void_p, _FP, _FP, _FP, _FP, _FP, c_int, c_int, c_int, c_int, c_int,
+                          _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
+    "tcw_clean_points": (c_int, [c_void_p, _FP, _FP, c_int, c_int, c_int, _VP, _VP, c_void_p]),
+}
+
+_lib = None
+
+
+class TcwError(RuntimeError):
+    pass
+
+
+def load() -> ctypes.CDLL:
+    """Load libtcwarp.so; raise (never fall back) if it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise TcwError(
+            f"{LIB_PATH} is missing: the CUDA library has not been built. Run "
+            "`python -c 'import __graft_entry__ as g; g.build()'` (or trajectorycrafter_b200/build.py). "
+            "There is no CPU or torch fallback for this path.")
+    lib = ctypes.CDLL(LIB_PATH)
+    for name, (res, args) in SIGNATURES.items():
+        fn = getattr(lib, name)          # AttributeError if the .so does not export a declared symbol
+        fn.restype = res
+        fn.argtypes = args
+    if lib.tcw_version() != 100:
+        raise TcwError(f"libtcwarp.so version {lib.tcw_version()} does not match the Python host (100)")
+    _lib = lib
+    return lib
+
+
+def check(rc: int, what: str) -> None:
+    if rc != 0:
+        msg = load().tcw_last_error()
+        raise TcwError(f"{what} failed (rc={rc}): {msg.decode() if msg else ''}")

@@ -1,0 +1,706 @@
+// tcwarp.cu — sm_100a kernels + C ABI (include/tcwarp.h) for the forward re-rendering path.
+//
+// Reference behaviour restated here: /root/reference/models/utils.py
+//   compute_transformed_points :350-420, forward_warp :220-293, bilinear_splatting :422-583,
+//   clean_points :585-626.  See DESIGN.md for the data layout and the per-kernel rooflines.
+//
+// Numerical contract: the per-pixel projection is evaluated with explicitly
+// un-fused, round-to-nearest fp32 operations in the reference's order (__fmul_rn/__fadd_rn/
+// __fdiv_rn are never contracted into FMAs), so flow12 and the integer corner indices are
+// bit-identical to the reference's CPU torch result.  This TU is also compiled with -fmad=false.
+#include "tcwarp.h"
+
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <stdlib.h>
+#include <string.h>
+
+#define TCW_API extern "C" __attribute__((visibility("default")))
+
+// ----------------------------------------------------------------------------------------------
+// errors / context
+// ----------------------------------------------------------------------------------------------
+static thread_local char g_err[512] = "";
+
+static int fail(int code, const char* fmt, const char* a = "", const char* b = "") {
+    snprintf(g_err, sizeof(g_err), fmt, a, b);
+    return code;
+}
+#define CUDA_TRY(expr)                                                                   \
+    do {                                                                                 \
+        cudaError_t e__ = (expr);                                                        \
+        if (e__ != cudaSuccess) return fail(TCW_E_CUDA, "%s failed: %s", #expr, cudaGetErrorString(e__)); \
+    } while (0)
+
+struct tcw_ctx {
+    int device;
+    int sm_count;
+    size_t l2_bytes;
+    long long launches;
+    int chunk_units_override;   // TCW_CHUNK_UNITS env (0 = auto)
+    // resources of the host-buffer entry point (grow-only)
+    cudaStream_t s_in, s_run, s_out;
+    void* pool;
+    size_t pool_bytes;
+};
+
+TCW_API int tcw_version(void) { return TCW_VERSION; }
+TCW_API const char* tcw_last_error(void) { return g_err; }
+TCW_API long long tcw_launch_count(const tcw_ctx* ctx) { return ctx ? ctx->launches : 0; }
+
+TCW_API int tcw_create(int device, tcw_ctx** out) {
+    if (!out) return fail(TCW_E_ARG, "tcw_create: out is NULL");
+    int n = 0;
+    CUDA_TRY(cudaGetDeviceCount(&n));
+    if (device < 0 || device >= n) return fail(TCW_E_ARG, "tcw_create: no such CUDA device");
+    cudaDeviceProp p;
+    CUDA_TRY(cudaGetDeviceProperties(&p, device));
+    tcw_ctx* c = (tcw_ctx*)calloc(1, sizeof(tcw_ctx));
+    if (!c) return fail(TCW_E_NOMEM, "tcw_create: out of host memory");
+    c->device = device;
+    c->sm_count = p.multiProcessorCount;
+    c->l2_bytes = (size_t)p.l2CacheSize;
+    const char* env = getenv("TCW_CHUNK_UNITS");
+    c->chunk_units_override = env ? atoi(env) : 0;
+    *out = c;
+    return TCW_OK;
+}
+
+TCW_API void tcw_destroy(tcw_ctx* c) {
+    if (!c) return;
+    int prev = 0;
+    cudaGetDevice(&prev);
+    cudaSetDevice(c->device);
+    if (c->pool) cudaFree(c->pool);
+    if (c->s_in) cudaStreamDestroy(c->s_in);
+    if (c->s_run) cudaStreamDestroy(c->s_run);
+    if (c->s_out) cudaStreamDestroy(c->s_out);
+    cudaSetDevice(prev);
+    free(c);
+}
+
+// ----------------------------------------------------------------------------------------------
+// device helpers
+// ----------------------------------------------------------------------------------------------
+constexpr int M_FLOATS = 30;
+constexpr int TILE_W = 32, TILE_H = 8, TILE_THREADS = TILE_W * TILE_H;
+constexpr int NCH = 5;   // accumulator planes: sum w*r, w*g, w*b, w*z, w
+
+__device__ __forceinline__ float dot3(const float* m, float a, float b, float c) {
+    // acc = 0; acc += m[k]*v[k]  — the reference's matmul order, never fused (models/utils.py:388,399)
+    float acc = __fadd_rn(0.0f, __fmul_rn(m[0], a));
+    acc = __fadd_rn(acc, __fmul_rn(m[1], b));
+    acc = __fadd_rn(acc, __fmul_rn(m[2], c));
+    return acc;
+}
+__device__ __forceinline__ float dot4(const float* m, float a, float b, float c, float d) {
+    float acc = __fadd_rn(0.0f, __fmul_rn(m[0], a));
+    acc = __fadd_rn(acc, __fmul_rn(m[1], b));
+    acc = __fadd_rn(acc, __fmul_rn(m[2], c));
+    acc = __fadd_rn(acc, __fmul_rn(m[3], d));
+    return acc;
+}
+
+// compute_transformed_points for one pixel (models/utils.py:388-417). M = K1inv | T[:3] | K2.
+__device__ __forceinline__ void project_px(const float* M, float fx, float fy, float d,
+                                           float& P0, float& P1, float& P2) {
+    float u0 = dot3(M + 0, fx, fy, 1.0f);
+    float u1 = dot3(M + 3, fx, fy, 1.0f);
+    float u2 = dot3(M + 6, fx, fy, 1.0f);
+    float X0 = __fmul_rn(d, u0), X1 = __fmul_rn(d, u1), X2 = __fmul_rn(d, u2);
+    float Y0 = dot4(M + 9, X0, X1, X2, 1.0f);
+    float Y1 = dot4(M + 13, X0, X1, X2, 1.0f);
+    float Y2 = dot4(M + 17, X0, X1, X2, 1.0f);
+    P0 = dot3(M + 21, Y0, Y1, Y2);
+    P1 = dot3(M + 24, Y0, Y1, Y2);
+    P2 = dot3(M + 27, Y0, Y1, Y2);
+    if (Y2 <= 0.01f) { P0 = 1000.0f; P1 = 1000.0f; P2 = 1000.0f; }   // behind the camera :404-417
+}
+
+__device__ __forceinline__ float clampf(float v, float lo, float hi) { return fminf(fmaxf(v, lo), hi); }
+
+// log(1 + clamp(z, 0, 1000))   (models/utils.py:490-491)
+__device__ __forceinline__ float log_depth(float z) { return logf(__fadd_rn(1.0f, clampf(z, 0.0f, 1000.0f))); }
+
+struct Corners {
+    int ix0, ix1, iy0, iy1;       // padded-grid indices in [0, w+1] x [0, h+1]
+    float nw, sw, ne, se;          // proximity weights
+};
+
+// indices and proximity weights from a flow vector (models/utils.py:450-488)
+__device__ __forceinline__ Corners corners_from_flow(float flx, float fly, int x, int y, int h, int w) {
+    float ox = __fadd_rn(__fadd_rn(flx, (float)x), 1.0f);
+    float oy = __fadd_rn(__fadd_rn(fly, (float)y), 1.0f);
+    const float wx = (float)(w + 1), hy = (float)(h + 1);
+    float fx0 = clampf(floorf(ox), 0.0f, wx), fx1 = clampf(ceilf(ox), 0.0f, wx);
+    float fy0 = clampf(floorf(oy), 0.0f, hy), fy1 = clampf(ceilf(oy), 0.0f, hy);
+    ox = clampf(ox, 0.0f, wx);
+    oy = clampf(oy, 0.0f, hy);
+    float ax = __fsub_rn(1.0f, __fsub_rn(ox, fx0)), bx = __fsub_rn(1.0f, __fsub_rn(fx1, ox));
+    float ay = __fsub_rn(1.0f, __fsub_rn(oy, fy0)), by = __fsub_rn(1.0f, __fsub_rn(fy1, oy));
+    Corners c;
+    c.ix0 = (int)fx0; c.ix1 = (int)fx1; c.iy0 = (int)fy0; c.iy1 = (int)fy1;
+    c.nw = __fmul_rn(ay, ax); c.sw = __fmul_rn(by, ax); c.ne = __fmul_rn(ay, bx); c.se = __fmul_rn(by, bx);
+    return c;
+}
+
+__device__ __forceinline__ float block_max_256(float v) {
+    __shared__ float red[TILE_THREADS / 32];
+    #pragma unroll
+    for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    if ((threadIdx.x & 31) == 0) red[threadIdx.x >> 5] = v;
+    __syncthreads();
+    if (threadIdx.x < 32) {
+        v = threadIdx.x < TILE_THREADS / 32 ? red[threadIdx.x] : 0.0f;
+        #pragma unroll
+        for (int o = 4; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+    }
+    return v;   // valid in thread 0
+}
+
+// ----------------------------------------------------------------------------------------------
+// K0: per-unit max of log(1+sat(z'))  — the soft-z normaliser  (models/utils.py:492)
+//   grid (tiles, n_units); reads depth only (4 B/px).
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TILE_THREADS)
+k_zmax(const float* __restrict__ depth, const int* __restrict__ src_index, const float* __restrict__ Mall,
+       int unit0, int h, int w, int tiles_x, unsigned* __restrict__ Lbits, int n_units_total) {
+    __shared__ float M[M_FLOATS];
+    const int u = unit0 + blockIdx.y;
+    if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
+    __syncthreads();
+    const int s = src_index ? src_index[u] : u;
+    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
+    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
+    float ld = 0.0f;
+    if (x < w && y < h) {
+        float d = depth[(size_t)s * h * w + (size_t)y * w + x];
+        float P0, P1, P2;
+        project_px(M, (float)x, (float)y, d, P0, P1, P2);
+        ld = log_depth(P2);
+    }
+    float m = block_max_256(ld);
+    if (threadIdx.x == 0) {
+        // ld >= 0, so the float order equals the unsigned order of the bit patterns
+        atomicMax(&Lbits[u], __float_as_uint(m));
+        atomicMax(&Lbits[n_units_total], __float_as_uint(m));
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// K2 (v1): fused unproject/transform/project + bilinear soft-z splat, fp32 L2 reductions.
+//   acc: [unit in chunk][NCH][h*w] fp32, pad ring dropped (it is cropped at :568-569).
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TILE_THREADS)
+k_project_splat_f32(const float* __restrict__ frame, const float* __restrict__ mask1,
+                    const float* __restrict__ depth, const int* __restrict__ src_index,
+                    const float* __restrict__ Mall, int unit0, int h, int w, int tiles_x,
+                    const unsigned* __restrict__ Lbits, int l_index_global /* -1: per unit */,
+                    float* __restrict__ acc, float* __restrict__ out_flow) {
+    __shared__ float M[M_FLOATS];
+    const int uc = blockIdx.y, u = unit0 + uc;
+    if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
+    __syncthreads();
+    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
+    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
+    if (x >= w || y >= h) return;
+    const int s = src_index ? src_index[u] : u;
+    const size_t hw = (size_t)h * w, p = (size_t)y * w + x;
+    const float d = depth[(size_t)s * hw + p];
+    float P0, P1, P2;
+    project_px(M, (float)x, (float)y, d, P0, P1, P2);
+    // coords = P.xy / P.z ; flow12 = coords - grid   (models/utils.py:273-278)
+    const float flx = __fsub_rn(__fdiv_rn(P0, P2), (float)x);
+    const float fly = __fsub_rn(__fdiv_rn(P1, P2), (float)y);
+    if (out_flow) {
+        out_flow[(size_t)u * 2 * hw + p] = flx;
+        out_flow[(size_t)u * 2 * hw + hw + p] = fly;
+    }
+    const Corners c = corners_from_flow(flx, fly, x, y, h, w);
+    const float L = __uint_as_float(Lbits[l_index_global >= 0 ? l_index_global : u]);
+    const float g = expf(__fmul_rn(__fdiv_rn(log_depth(P2), L), 50.0f));   // :492
+    const float m = mask1 ? mask1[(size_t)s * hw + p] : 1.0f;
+    const float r = frame[((size_t)s * 3 + 0) * hw + p];
+    const float gch = frame[((size_t)s * 3 + 1) * hw + p];
+    const float b = frame[((size_t)s * 3 + 2) * hw + p];
+    float* a = acc + (size_t)uc * NCH * hw;
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int cx = (k & 2) ? c.ix1 : c.ix0;
+        const int cy = (k & 1) ? c.iy1 : c.iy0;
+        if (cx < 1 || cx > w || cy < 1 || cy > h) continue;          // pad ring: cropped away
+        const float prox = k == 0 ? c.nw : (k == 1 ? c.sw : (k == 2 ? c.ne : c.se));
+        const float wk = __fdiv_rn(__fmul_rn(prox, m), g);            // :494-513
+        const size_t cell = (size_t)(cy - 1) * w + (cx - 1);
+        atomicAdd(a + 0 * hw + cell, __fmul_rn(r, wk));
+        atomicAdd(a + 1 * hw + cell, __fmul_rn(gch, wk));
+        atomicAdd(a + 2 * hw + cell, __fmul_rn(b, wk));
+        atomicAdd(a + 3 * hw + cell, __fmul_rn(P2, wk));
+        atomicAdd(a + 4 * hw + cell, wk);
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// K3: normalise / mask / clip (+ optional fused clean_points)   (models/utils.py:566-583, 585-626)
+// ----------------------------------------------------------------------------------------------
+template <bool CLEAN>
+__global__ void __launch_bounds__(TILE_THREADS)
+k_normalise(const float* __restrict__ acc, int unit0, int h, int w, int tiles_x,
+            void* __restrict__ out_frame, void* __restrict__ out_mask, float* __restrict__ out_depth,
+            int* __restrict__ range_flag) {
+    const int uc = blockIdx.y, u = unit0 + uc;
+    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
+    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
+    if (x >= w || y >= h) return;
+    const size_t hw = (size_t)h * w, p = (size_t)y * w + x;
+    const float* a = acc + (size_t)uc * NCH * hw;
+    const float W = a[4 * hw + p];
+    const bool valid = W > 0.0f;
+    float col[3];
+    bool bad = false;
+    #pragma unroll
+    for (int ch = 0; ch < 3; ++ch) {
+        float v = valid ? __fdiv_rn(a[ch * hw + p], W) : -1.0f;
+        bad |= !(v >= -1.1f) || !(v <= 1.1f);
+        col[ch] = clampf(v, -1.0f, 1.0f);
+    }
+    if (bad && range_flag) atomicOr(range_flag, 1);
+    if (out_depth) out_depth[(size_t)u * hw + p] = valid ? __fdiv_rn(a[3 * hw + p], W) : 0.0f;
+    if (!CLEAN) {
+        float* of = (float*)out_frame;
+        #pragma unroll
+        for (int ch = 0; ch < 3; ++ch) of[((size_t)u * 3 + ch) * hw + p] = col[ch];
+        ((float*)out_mask)[(size_t)u * hw + p] = valid ? 1.0f : 0.0f;
+    } else {
+        // clean_points: hole mask dilated 5x5 (outside pixels never win), float64 outputs
+        bool hole = false;
+        #pragma unroll
+        for (int dy = -2; dy <= 2; ++dy) {
+            const int yy = y + dy;
+            if (yy < 0 || yy >= h) continue;
+            #pragma unroll
+            for (int dx = -2; dx <= 2; ++dx) {
+                const int xx = x + dx;
+                if (xx < 0 || xx >= w) continue;
+                hole |= !(a[4 * hw + (size_t)yy * w + xx] > 0.0f);
+            }
+        }
+        const double keep = hole ? 0.0 : 1.0;
+        double* of = (double*)out_frame;
+        #pragma unroll
+        for (int ch = 0; ch < 3; ++ch) {
+            const float half = __fdiv_rn(__fadd_rn(col[ch], 1.0f), 2.0f);
+            of[((size_t)u * 3 + ch) * hw + p] = __dsub_rn(__dmul_rn(__dmul_rn((double)half, keep), 2.0), 1.0);
+        }
+        ((double*)out_mask)[(size_t)u * hw + p] = keep;
+    }
+}
+
+// ----------------------------------------------------------------------------------------------
+// compute_transformed_points as a standalone op
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TILE_THREADS)
+k_project(const float* __restrict__ depth, const int* __restrict__ src_index, const float* __restrict__ Mall,
+          int h, int w, int tiles_x, float* __restrict__ out) {
+    __shared__ float M[M_FLOATS];
+    const int u = blockIdx.y;
+    if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
+    __syncthreads();
+    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
+    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
+    if (x >= w || y >= h) return;
+    const int s = src_index ? src_index[u] : u;
+    const size_t hw = (size_t)h * w, p = (size_t)y * w + x;
+    float P0, P1, P2;
+    project_px(M, (float)x, (float)y, depth[(size_t)s * hw + p], P0, P1, P2);
+    float* o = out + ((size_t)u * hw + p) * 3;
+    o[0] = P0; o[1] = P1; o[2] = P2;
+}
+
+// ----------------------------------------------------------------------------------------------
+// generic bilinear_splatting (models/utils.py:422-583), c in 1..4
+// ----------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(TILE_THREADS)
+k_logmax(const float* __restrict__ depth, size_t hw, unsigned* __restrict__ Lbits, int b_total) {
+    const int n = blockIdx.y;
+    float ld = 0.0f;
+    for (size_t i = (size_t)blockIdx.x * TILE_THREADS + threadIdx.x; i < hw; i += (size_t)gridDim.x * TILE_THREADS)
+        ld = fmaxf(ld, log_depth(depth[(size_t)n * hw + i]));
+    float m = block_max_256(ld);
+    if (threadIdx.x == 0) {
+        atomicMax(&Lbits[n], __float_as_uint(m));
+        atomicMax(&Lbits[b_total], __float_as_uint(m));
+    }
+}
+
+template <int C>
+__global__ void __launch_bounds__(TILE_THREADS)
+k_splat_f32(const float* __restrict__ frame, const float* __restrict__ mask1, const float* __restrict__ depth,
+            const float* __restrict__ flow, const float* __restrict__ flow_mask, int unit0, int h, int w,
+            int tiles_x, const unsigned* __restrict__ Lbits, int l_index_global, float* __restrict__ acc) {
+    const int uc = blockIdx.y, n = unit0 + uc;
+    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
+    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
+    if (x >= w || y >= h) return;
+    const size_t hw = (size_t)h * w, p = (size_t)y * w + x;
+    const Corners c = corners_from_flow(flow[(size_t)n * 2 * hw + p], flow[(size_t)n * 2 * hw + hw + p], x, y, h, w);
+    const float L = __uint_as_float(Lbits[l_index_global >= 0 ? l_index_global : n]);
+    const float g = expf(__fmul_rn(__fdiv_rn(log_depth(depth[(size_t)n * hw + p]), L), 50.0f));
+    const float m = mask1 ? mask1[(size_t)n * hw + p] : 1.0f;
+    const float fm = flow_mask ? flow_mask[(size_t)n * hw + p] : 1.0f;
+    float v[C];
+    #pragma unroll
+    for (int ch = 0; ch < C; ++ch) v[ch] = frame[((size_t)n * C + ch) * hw + p];
+    float* a = acc + (size_t)uc * (C + 1) * hw;
+    #pragma unroll
+    for (int k = 0; k < 4; ++k) {
+        const int cx = (k & 2) ? c.ix1 : c.ix0;
+        const int cy = (k & 1) ? c.iy1 : c.iy0;
+        if (cx < 1 || cx > w || cy < 1 || cy > h) continue;
+        const float prox = k == 0 ? c.nw : (k == 1 ? c.sw : (k == 2 ? c.ne : c.se));
+        const float wk = __fdiv_rn(__fmul_rn(__fmul_rn(prox, m), fm), g);
+        const size_t cell = (size_t)(cy - 1) * w + (cx - 1);
+        #pragma unroll
+        for (int ch = 0; ch < C; ++ch) atomicAdd(a + ch * hw + cell, __fmul_rn(v[ch], wk));
+        atomicAdd(a + C * hw + cell, wk);
+    }
+}
+
+template <int C>
+__global__ void __launch_bounds__(TILE_THREADS)
+k_splat_normalise(const float* __restrict__ acc, int unit0, size_t hw, int is_image,
+                  float* __restrict__ out, float* __restrict__ out_mask, int* __restrict__ range_flag) {
+    const int uc = blockIdx.y, n = unit0 + uc;
+    const size_t p = (size_t)blockIdx.x * TILE_THREADS + threadIdx.x;
+    if (p >= hw) return;
+    const float* a = acc + (size_t)uc * (C + 1) * hw;
+    const float W = a[C * hw + p];
+    const bool valid = W > 0.0f;
+    bool bad = false;
+    #pragma unroll
+    for (int ch = 0; ch < C; ++ch) {
+        float v = valid ? __fdiv_rn(a[ch * hw + p], W) : (is_image ? -1.0f : 0.0f);
+        if (is_image) {
+            bad |= !(v >= -1.1f) || !(v <= 1.1f);
+            v = clampf(v, -1.0f, 1.0f);
+        }
+        out[((size_t)n * C + ch) * hw + p] = v;
+    }
+    if (bad && range_flag) atomicOr(range_flag, 1);
+    out_mask[(size_t)n * hw + p] = valid ? 1.0f : 0.0f;
+}
+
+// standalone clean_points (models/utils.py:585-626)
+__global__ void __launch_bounds__(TILE_THREADS)
+k_clean_points(const float* __restrict__ frame, const float* __restrict__ mask2, int c, int h, int w, int tiles_x,
+               double* __restrict__ out_frame, double* __restrict__ out_mask) {
+    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
+    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
+    if (x >= w || y >= h) return;
+    const size_t hw = (size_t)h * w, p = (size_t)y * w + x;
+    bool hole = false;
+    for (int dy = -2; dy <= 2; ++dy) {
+        const int yy = y + dy;
+        if (yy < 0 || yy >= h) continue;
+        for (int dx = -2; dx <= 2; ++dx) {
+            const int xx = x + dx;
+            if (xx < 0 || xx >= w) continue;
+            hole |= __fsub_rn(1.0f, mask2[(size_t)yy * w + xx]) >= 0.5f;
+        }
+    }
+    const double keep = hole ? 0.0 : 1.0;
+    for (int ch = 0; ch < c; ++ch) {
+        const float half = __fdiv_rn(__fadd_rn(frame[(size_t)ch * hw + p], 1.0f), 2.0f);
+        out_frame[(size_t)ch * hw + p] = __dsub_rn(__dmul_rn(__dmul_rn((double)half, keep), 2.0), 1.0);
+    }
+    out_mask[p] = keep;
+}
+
+// ----------------------------------------------------------------------------------------------
+// host side of the C ABI
+// ----------------------------------------------------------------------------------------------
+static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
+static size_t header_bytes(int n_units) { return align_up((size_t)(n_units + 1) * sizeof(unsigned), 256); }
+
+// units per chunk: keep one chunk's accumulators + inputs + outputs (~64 B/px) inside L2
+static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, int planes) {
+    if (ctx->chunk_units_override > 0) return ctx->chunk_units_override < n_units ? ctx->chunk_units_override : n_units;
+    const size_t per_unit = (size_t)h * w * (size_t)(4 * planes + 44);
+    size_t budget = ctx->l2_bytes ? ctx->l2_bytes * 6 / 10 : (size_t)64 << 20;
+    int g = (int)(budget / per_unit);
+    if (g < 1) g = 1;
+    return g < n_units ? g : n_units;
+}
+
+TCW_API int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, int flags, size_t* bytes) {
+    (void)flags;
+    if (!ctx || !bytes || n_units <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_workspace_bytes: bad argument");
+    const int g = auto_chunk_units(ctx, n_units, h, w, NCH);
+    *bytes = header_bytes(n_units) + (size_t)g * NCH * h * w * sizeof(float);
+    return TCW_OK;
+}
+
+static int check_launch(tcw_ctx* ctx, const char* what) {
+    ctx->launches++;
+    cudaError_t e = cudaGetLastError();
+    if (e != cudaSuccess) return fail(TCW_E_CUDA, "launch of %s failed: %s", what, cudaGetErrorString(e));
+    return TCW_OK;
+}
+#define LAUNCH_CHECK(what) do { int rc__ = check_launch(ctx, what); if (rc__) return rc__; } while (0)
+
+TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                             const int* src_index, const float* M, int n_units, int n_src, int h, int w,
+                             int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                             int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp: ctx is NULL");
+    if (!frame || !depth || !M || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_forward_warp: NULL buffer");
+    if (n_units <= 0 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp: bad shape");
+    if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp: src_index is NULL but n_src != n_units");
+    if (flags & TCW_DETERMINISTIC) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_DETERMINISTIC not available in this build");
+    const size_t hw = (size_t)h * w;
+    const size_t hdr = header_bytes(n_units);
+    if (!workspace || workspace_bytes < hdr + NCH * hw * sizeof(float))
+        return fail(TCW_E_WORKSPACE, "tcw_forward_warp: workspace too small (see tcw_workspace_bytes)");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    int g = (int)((workspace_bytes - hdr) / (NCH * hw * sizeof(float)));
+    const int want = auto_chunk_units(ctx, n_units, h, w, NCH);
+    if (g > want) g = want;
+    unsigned* Lbits = (unsigned*)workspace;
+    float* acc = (float*)((char*)workspace + hdr);
+    const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
+    const bool per_unit = flags & TCW_PER_UNIT_MAX;
+    CUDA_TRY(cudaMemsetAsync(Lbits, 0, hdr, st));
+    if (!per_unit) {   // the call-wide max needs every unit's depth pass first
+        for (int u0 = 0; u0 < n_units; u0 += 65535) {
+            const int nu = n_units - u0 < 65535 ? n_units - u0 : 65535;
+            k_zmax<<<dim3(tiles_x * tiles_y, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, Lbits, n_units);
+            LAUNCH_CHECK("k_zmax");
+        }
+    }
+    for (int u0 = 0; u0 < n_units; u0 += g) {
+        const int nu = n_units - u0 < g ? n_units - u0 : g;
+        const dim3 grid(tiles_x * tiles_y, nu);
+        CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)nu * NCH * hw * sizeof(float), st));
+        if (per_unit) {
+            k_zmax<<<grid, TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, Lbits, n_units);
+            LAUNCH_CHECK("k_zmax");
+        }
+        k_project_splat_f32<<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
+                                                          Lbits, per_unit ? -1 : n_units, acc, out_flow);
+        LAUNCH_CHECK("k_project_splat_f32");
+        if (flags & TCW_CLEAN)
+            k_normalise<true><<<grid, TILE_THREADS, 0, st>>>(acc, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
+        else
+            k_normalise<false><<<grid, TILE_THREADS, 0, st>>>(acc, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
+        LAUNCH_CHECK("k_normalise");
+    }
+    return TCW_OK;
+}
+
+TCW_API int tcw_project(tcw_ctx* ctx, const float* depth, const int* src_index, const float* M,
+                        int n_units, int n_src, int h, int w, float* out_points, void* cuda_stream) {
+    if (!ctx || !depth || !M || !out_points) return fail(TCW_E_ARG, "tcw_project: NULL argument");
+    if (n_units <= 0 || n_units > 65535 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_project: bad shape");
+    if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_project: src_index is NULL but n_src != n_units");
+    const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
+    k_project<<<dim3(tiles_x * tiles_y, n_units), TILE_THREADS, 0, (cudaStream_t)cuda_stream>>>(depth, src_index, M, h, w, tiles_x, out_points);
+    LAUNCH_CHECK("k_project");
+    return TCW_OK;
+}
+
+template <int C>
+static int splat_c(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth, const float* flow,
+                   const float* flow_mask, int b, int h, int w, int flags, float* out, float* out_mask,
+                   int* range_flag, void* workspace, size_t workspace_bytes, cudaStream_t st) {
+    const size_t hw = (size_t)h * w;
+    const size_t hdr = header_bytes(b);
+    if (!workspace || workspace_bytes < hdr + (C + 1) * hw * sizeof(float))
+        return fail(TCW_E_WORKSPACE, "tcw_splat: workspace too small (see tcw_workspace_bytes)");
+    int g = (int)((workspace_bytes - hdr) / ((C + 1) * hw * sizeof(float)));
+    const int want = auto_chunk_units(ctx, b, h, w, C + 1);
+    if (g > want) g = want;
+    unsigned* Lbits = (unsigned*)workspace;
+    float* acc = (float*)((char*)workspace + hdr);
+    const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
+    const bool per_unit = flags & TCW_PER_UNIT_MAX;
+    CUDA_TRY(cudaMemsetAsync(Lbits, 0, hdr, st));
+    int red_blocks = (int)((hw + TILE_THREADS * 8 - 1) / (TILE_THREADS * 8));
+    if (red_blocks < 1) red_blocks = 1;
+    k_logmax<<<dim3(red_blocks, b), TILE_THREADS, 0, st>>>(depth, hw, Lbits, b);
+    LAUNCH_CHECK("k_logmax");
+    for (int u0 = 0; u0 < b; u0 += g) {
+        const int nu = b - u0 < g ? b - u0 : g;
+        CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)nu * (C + 1) * hw * sizeof(float), st));
+        k_splat_f32<C><<<dim3(tiles_x * tiles_y, nu), TILE_THREADS, 0, st>>>(frame, mask1, depth, flow, flow_mask, u0, h, w,
+                                                                           tiles_x, Lbits, per_unit ? -1 : b, acc);
+        LAUNCH_CHECK("k_splat_f32");
+        k_splat_normalise<C><<<dim3((unsigned)((hw + TILE_THREADS - 1) / TILE_THREADS), nu), TILE_THREADS, 0, st>>>(
+            acc, u0, hw, (flags & TCW_IS_IMAGE) ? 1 : 0, out, out_mask, range_flag);
+        LAUNCH_CHECK("k_splat_normalise");
+    }
+    return TCW_OK;
+}
+
+TCW_API int tcw_splat(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                      const float* flow, const float* flow_mask, int b, int c, int h, int w, int flags,
+                      float* out, float* out_mask, int* range_flag, void* workspace, size_t workspace_bytes,
+                      void* cuda_stream) {
+    if (!ctx || !frame || !depth || !flow || !out || !out_mask) return fail(TCW_E_ARG, "tcw_splat: NULL argument");
+    if (b <= 0 || b > 65535 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_splat: bad shape");
+    if (flags & TCW_DETERMINISTIC) return fail(TCW_E_ARG, "tcw_splat: TCW_DETERMINISTIC not available in this build");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    switch (c) {
+        case 1: return splat_c<1>(ctx, frame, mask1, depth, flow, flow_mask, b, h, w, flags, out, out_mask, range_flag, workspace, workspace_bytes, st);
+        case 2: return splat_c<2>(ctx, frame, mask1, depth, flow, flow_mask, b, h, w, flags, out, out_mask, range_flag, workspace, workspace_bytes, st);
+        case 3: return splat_c<3>(ctx, frame, mask1, depth, flow, flow_mask, b, h, w, flags, out, out_mask, range_flag, workspace, workspace_bytes, st);
+        case 4: return splat_c<4>(ctx, frame, mask1, depth, flow, flow_mask, b, h, w, flags, out, out_mask, range_flag, workspace, workspace_bytes, st);
+        default: return fail(TCW_E_ARG, "tcw_splat: c must be 1..4");
+    }
+}
+
+TCW_API int tcw_clean_points(tcw_ctx* ctx, const float* frame, const float* mask2, int c, int h, int w,
+                             double* out_frame, double* out_mask, void* cuda_stream) {
+    if (!ctx || !frame || !mask2 || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_clean_points: NULL argument");
+    if (c < 1 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_clean_points: bad shape");
+    const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
+    k_clean_points<<<tiles_x * tiles_y, TILE_THREADS, 0, (cudaStream_t)cuda_stream>>>(frame, mask2, c, h, w, tiles_x, out_frame, out_mask);
+    LAUNCH_CHECK("k_clean_points");
+    return TCW_OK;
+}
+
+// ----------------------------------------------------------------------------------------------
+// host-buffer entry: upload -> warp -> download, pipelined over three streams
+// ----------------------------------------------------------------------------------------------
+static int ensure_host_resources(tcw_ctx* ctx, size_t need) {
+    if (!ctx->s_in) {
+        CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_in, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_run, cudaStreamNonBlocking));
+        CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_out, cudaStreamNonBlocking));
+    }
+    if (ctx->pool_bytes < need) {
+        if (ctx->pool) { CUDA_TRY(cudaFree(ctx->pool)); ctx->pool = nullptr; ctx->pool_bytes = 0; }
+        cudaError_t e = cudaMalloc(&ctx->pool, need);
+        if (e != cudaSuccess) return fail(TCW_E_NOMEM, "tcw_forward_warp_host: cudaMalloc failed: %s", cudaGetErrorString(e));
+        ctx->pool_bytes = need;
+    }
+    return TCW_OK;
+}
+
+TCW_API int tcw_forward_warp_host(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                                  const int* src_index, const float* M, int n_units, int n_src, int h, int w,
+                                  int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                                  int* range_flag) {
+    if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp_host: ctx is NULL");
+    if (!frame || !depth || !M || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_forward_warp_host: NULL buffer");
+    if (n_units <= 0 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp_host: bad shape");
+    if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp_host: src_index is NULL but n_src != n_units");
+    if (src_index) for (int u = 0; u < n_units; ++u)
+        if (src_index[u] < 0 || src_index[u] >= n_src) return fail(TCW_E_ARG, "tcw_forward_warp_host: src_index out of range");
+    int prev = 0;
+    CUDA_TRY(cudaGetDevice(&prev));
+    CUDA_TRY(cudaSetDevice(ctx->device));
+    const size_t hw = (size_t)h * w, fb = sizeof(float);
+    const size_t esz = (flags & TCW_CLEAN) ? sizeof(double) : sizeof(float);
+    size_t ws_bytes = 0;
+    int rc = tcw_workspace_bytes(ctx, n_units, h, w, flags, &ws_bytes);
+    if (rc) return rc;
+    // pool layout
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
+    const size_t o_frame = take((size_t)n_src * 3 * hw * fb), o_depth = take((size_t)n_src * hw * fb);
+    const size_t o_mask1 = mask1 ? take((size_t)n_src * hw * fb) : 0;
+    const size_t o_M = take((size_t)n_units * M_FLOATS * fb), o_si = take((size_t)n_units * sizeof(int));
+    const size_t o_flag = take(256);
+    const size_t o_of = take((size_t)n_units * 3 * hw * esz), o_om = take((size_t)n_units * hw * esz);
+    const size_t o_od = out_depth ? take((size_t)n_units * hw * fb) : 0;
+    const size_t o_ofl = out_flow ? take((size_t)n_units * 2 * hw * fb) : 0;
+    const size_t o_ws = take(ws_bytes);
+    rc = ensure_host_resources(ctx, off);
+    if (rc) return rc;
+    char* base = (char*)ctx->pool;
+    float* d_frame = (float*)(base + o_frame); float* d_depth = (float*)(base + o_depth);
+    float* d_mask1 = mask1 ? (float*)(base + o_mask1) : nullptr;
+    float* d_M = (float*)(base + o_M); int* d_si = src_index ? (int*)(base + o_si) : nullptr;
+    int* d_flag = (int*)(base + o_flag);
+    char* d_of = base + o_of; char* d_om = base + o_om;
+    float* d_od = out_depth ? (float*)(base + o_od) : nullptr;
+    float* d_ofl = out_flow ? (float*)(base + o_ofl) : nullptr;
+
+    // slices of units: upload the sources a slice needs, run it, download its outputs
+    const int slice = auto_chunk_units(ctx, n_units, h, w, NCH) * 2;
+    const int n_slices = (n_units + slice - 1) / slice;
+    cudaEvent_t* ev_in = (cudaEvent_t*)calloc((size_t)n_slices * 2, sizeof(cudaEvent_t));
+    if (!ev_in) return fail(TCW_E_NOMEM, "tcw_forward_warp_host: out of host memory");
+    cudaEvent_t* ev_run = ev_in + n_slices;
+    for (int i = 0; i < 2 * n_slices; ++i) CUDA_TRY(cudaEventCreateWithFlags(&ev_in[i], cudaEventDisableTiming));
+
+    CUDA_TRY(cudaMemcpyAsync(d_M, M, (size_t)n_units * M_FLOATS * fb, cudaMemcpyHostToDevice, ctx->s_in));
+    if (src_index) CUDA_TRY(cudaMemcpyAsync(d_si, src_index, (size_t)n_units * sizeof(int), cudaMemcpyHostToDevice, ctx->s_in));
+    CUDA_TRY(cudaMemsetAsync(d_flag, 0, sizeof(int), ctx->s_in));
+    int uploaded = 0;   // sources [0, uploaded) are queued on s_in
+    for (int i = 0; i < n_slices; ++i) {
+        const int u0 = i * slice, nu = n_units - u0 < slice ? n_units - u0 : slice;
+        int need = 0;
+        for (int u = u0; u < u0 + nu; ++u) { int s = src_index ? src_index[u] : u; if (s + 1 > need) need = s + 1; }
+        if (need > uploaded) {
+            const size_t a = uploaded, n = need - uploaded;
+            CUDA_TRY(cudaMemcpyAsync(d_frame + a * 3 * hw, frame + a * 3 * hw, n * 3 * hw * fb, cudaMemcpyHostToDevice, ctx->s_in));
+            CUDA_TRY(cudaMemcpyAsync(d_depth + a * hw, depth + a * hw, n * hw * fb, cudaMemcpyHostToDevice, ctx->s_in));
+            if (mask1) CUDA_TRY(cudaMemcpyAsync(d_mask1 + a * hw, mask1 + a * hw, n * hw * fb, cudaMemcpyHostToDevice, ctx->s_in));
+            uploaded = need;
+        }
+        CUDA_TRY(cudaEventRecord(ev_in[i], ctx->s_in));
+        CUDA_TRY(cudaStreamWaitEvent(ctx->s_run, ev_in[i], 0));
+        if (!(flags & TCW_PER_UNIT_MAX) && i == 0 && uploaded < n_src) {
+            // call-wide max needs every source before the first splat: upload the rest now
+            const size_t a = uploaded, n = n_src - uploaded;
+            CUDA_TRY(cudaMemcpyAsync(d_frame + a * 3 * hw, frame + a * 3 * hw, n * 3 * hw * fb, cudaMemcpyHostToDevice, ctx->s_in));
+            CUDA_TRY(cudaMemcpyAsync(d_depth + a * hw, depth + a * hw, n * hw * fb, cudaMemcpyHostToDevice, ctx->s_in));
+            if (mask1) CUDA_TRY(cudaMemcpyAsync(d_mask1 + a * hw, mask1 + a * hw, n * hw * fb, cudaMemcpyHostToDevice, ctx->s_in));
+            uploaded = n_src;
+            CUDA_TRY(cudaEventRecord(ev_in[i], ctx->s_in));
+            CUDA_TRY(cudaStreamWaitEvent(ctx->s_run, ev_in[i], 0));
+        }
+        if (flags & TCW_PER_UNIT_MAX) {
+            const float *sf = d_frame, *sd = d_depth, *sm = d_mask1;
+            int ns = n_src;
+            if (!d_si) {   // identity mapping: unit u reads source u, so offset the source pointers
+                sf += (size_t)u0 * 3 * hw; sd += (size_t)u0 * hw; if (sm) sm += (size_t)u0 * hw; ns = nu;
+            }
+            rc = tcw_forward_warp(ctx, sf, sm, sd, d_si ? d_si + u0 : nullptr, d_M + (size_t)u0 * M_FLOATS,
+                                  nu, ns, h, w, flags,
+                                  d_of + (size_t)u0 * 3 * hw * esz, d_om + (size_t)u0 * hw * esz,
+                                  d_od ? d_od + (size_t)u0 * hw : nullptr, d_ofl ? d_ofl + (size_t)u0 * 2 * hw : nullptr,
+                                  d_flag, base + o_ws, ws_bytes, ctx->s_run);
+        } else if (i == 0) {
+            rc = tcw_forward_warp(ctx, d_frame, d_mask1, d_depth, d_si, d_M, n_units, n_src, h, w, flags,
+                                  d_of, d_om, d_od, d_ofl, d_flag, base + o_ws, ws_bytes, ctx->s_run);
+        }
+        if (rc) break;
+        CUDA_TRY(cudaEventRecord(ev_run[i], ctx->s_run));
+        if ((flags & TCW_PER_UNIT_MAX) || i == n_slices - 1) {
+            const int d0 = (flags & TCW_PER_UNIT_MAX) ? u0 : 0;
+            const int dn = (flags & TCW_PER_UNIT_MAX) ? nu : n_units;
+            CUDA_TRY(cudaStreamWaitEvent(ctx->s_out, ev_run[i], 0));
+            CUDA_TRY(cudaMemcpyAsync((char*)out_frame + (size_t)d0 * 3 * hw * esz, d_of + (size_t)d0 * 3 * hw * esz, (size_t)dn * 3 * hw * esz, cudaMemcpyDeviceToHost, ctx->s_out));
+            CUDA_TRY(cudaMemcpyAsync((char*)out_mask + (size_t)d0 * hw * esz, d_om + (size_t)d0 * hw * esz, (size_t)dn * hw * esz, cudaMemcpyDeviceToHost, ctx->s_out));
+            if (out_depth) CUDA_TRY(cudaMemcpyAsync(out_depth + (size_t)d0 * hw, d_od + (size_t)d0 * hw, (size_t)dn * hw * fb, cudaMemcpyDeviceToHost, ctx->s_out));
+            if (out_flow) CUDA_TRY(cudaMemcpyAsync(out_flow + (size_t)d0 * 2 * hw, d_ofl + (size_t)d0 * 2 * hw, (size_t)dn * 2 * hw * fb, cudaMemcpyDeviceToHost, ctx->s_out));
+        }
+    }
+    int flag_host = 0;
+    if (!rc) {
+        CUDA_TRY(cudaStreamSynchronize(ctx->s_run));
+        CUDA_TRY(cudaMemcpyAsync(&flag_host, d_flag, sizeof(int), cudaMemcpyDeviceToHost, ctx->s_out));
+        CUDA_TRY(cudaStreamSynchronize(ctx->s_out));
+        CUDA_TRY(cudaStreamSynchronize(ctx->s_in));
+    } else {
+        cudaDeviceSynchronize();
+    }
+    for (int i = 0; i < 2 * n_slices; ++i) cudaEventDestroy(ev_in[i]);
+    free(ev_in);
+    if (range_flag) *range_flag = flag_host;
+    cudaSetDevice(prev);
+    return rc;
+}

@@ -1,0 +1,343 @@
+"""``Warper`` — host-side mirror of the reference class (reference models/utils.py:213-682).
+
+Same constructor, method names, positional order, kwargs, return tuples and error behaviour as the
+reference; every tensor operation of the hot path is executed by libtcwarp.so (hand-written
+sm_100a CUDA behind include/tcwarp.h).  PyTorch is used for device memory, streams and the two
+tiny CPU matrix inverses only.  There is no CPU path: ``Warper(device='cpu')`` raises.
+
+Documented deviations from the reference:
+  * ``get_device``: the reference maps every string except ``'cpu'``/``'gpuN'`` — including the
+    ``'cuda:0'`` all its callers pass — to the CPU (models/utils.py:669-682).  Here ``'gpuN'``,
+    ``'cuda'`` and ``'cuda:N'`` all select that GPU and ``'cpu'`` is an error.
+  * outputs are contiguous NCHW tensors on the GPU (the reference returns non-contiguous views).
+"""
+from __future__ import annotations
+
+import ctypes
+from pathlib import Path
+from typing import Optional, Tuple
+
+import numpy
+import torch
+
+from . import _lib
+from .matrices import prepare_matrices
+
+
+def _ptr(t: Optional[torch.Tensor]) -> Optional[int]:
+    return None if t is None else t.data_ptr()
+
+
+class Warper:
+    def __init__(self, resolution: tuple = None, device: str = 'gpu0'):
+        self.resolution = resolution
+        self.device = self.get_device(device)
+        self.dtype = torch.float32
+        self._lib = _lib.load()            # raises if libtcwarp.so has not been built
+        self._ctx = None
+        self._workspace = None
+        return
+
+    # ------------------------------------------------------------------ plumbing
+    def _context(self) -> ctypes.c_void_p:
+        if self._ctx is None:
+            if not torch.cuda.is_available():
+                raise _lib.TcwError("no CUDA device is available and this path has no CPU fallback")
+            ctx = ctypes.c_void_p()
+            idx = self.device.index if self.device.index is not None else torch.cuda.current_device()
+            _lib.check(self._lib.tcw_create(idx, ctypes.byref(ctx)), "tcw_create")
+            self._ctx = ctx
+        return self._ctx
+
+    def __del__(self):
+        try:
+            if getattr(self, "_ctx", None) is not None:
+                self._lib.tcw_destroy(self._ctx)
+                self._ctx = None
+        except Exception:
+            pass
+
+    def _get_workspace(self, n_units: int, h: int, w: int, flags: int) -> torch.Tensor:
+        need = ctypes.c_size_t(0)
+        _lib.check(self._lib.tcw_workspace_bytes(self._context(), n_units, h, w, flags, ctypes.byref(need)),
+                   "tcw_workspace_bytes")
+        if self._workspace is None or self._workspace.numel() < need.value:
+            self._workspace = torch.empty(need.value, dtype=torch.uint8, device=self.device)
+        return self._workspace
+
+    def _stream(self) -> int:
+        return torch.cuda.current_stream(self.device).cuda_stream
+
+    def _dev(self, t: Optional[torch.Tensor]) -> Optional[torch.Tensor]:
+        if t is None:
+            return None
+        return t.to(self.device).to(self.dtype).contiguous()
+
+    def launch_count(self) -> int:
+        """Kernels launched by libtcwarp for this Warper so far (bench.py's gpu_launches)."""
+        return int(self._lib.tcw_launch_count(self._context()))
+
+    # ------------------------------------------------------------------ batched fast entry
+    def forward_warp_batch(self, frames: torch.Tensor, depths: torch.Tensor,
+                           transformation1: torch.Tensor, transformation2: torch.Tensor,
+                           intrinsic1: torch.Tensor, intrinsic2: Optional[torch.Tensor] = None,
+                           mask1: Optional[torch.Tensor] = None, src_index: Optional[torch.Tensor] = None,
+                           per_frame_max: bool = True, mask: bool = False,
+                           return_depth: bool = True, return_flow: bool = True, check_range: bool = True,
+                           deterministic: bool = False):
+        """All (source frame, pose) units of a clip in ONE submission.
+
+        Equivalent to looping the reference's ``forward_warp(frames[s:s+1], mask1[s:s+1],
+        depths[s:s+1], T1[u:u+1], T2[u:u+1], K1[u:u+1], K2[u:u+1], mask)`` over units u with
+        s = src_index[u] (demo.py:77-90, :203-231, :329-342) and concatenating the results — when
+        ``per_frame_max`` is True.  With False the soft-z normaliser is taken over the whole call
+        like one reference call with b = n_units (models/utils.py:492).
+        frames (n_src,3,h,w), depths (n_src,1,h,w), matrices (n_units,...).
+        Returns (warped (n,3,h,w), mask (n,1,h,w), depth (n,1,h,w)|None, flow12 (n,2,h,w)|None);
+        warped/mask are float64 when ``mask=True`` (reference quirk, models/utils.py:618-626).
+        """
+        n_src, c, h, w = frames.shape
+        n = transformation1.shape[0]
+        assert c == 3 and depths.shape == (n_src, 1, h, w)
+        if mask1 is not None:
+            assert mask1.shape == (n_src, 1, h, w)
+        if src_index is None:
+            assert n == n_src, "src_index is required when the number of poses differs from the number of frames"
+        M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
+        assert M.shape[0] == n
+        frames_d, depths_d, mask1_d = self._dev(frames), self._dev(depths), self._dev(mask1)
+        M_d = M.to(self.device, non_blocking=True)
+        si_d = None if src_index is None else src_index.to(self.device, torch.int32).contiguous()
+        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) \
+            | (_lib.TCW_DETERMINISTIC if deterministic else 0)
+        odt = torch.float64 if mask else torch.float32
+        out_frame = torch.empty((n, 3, h, w), dtype=odt, device=self.device)
+        out_mask = torch.empty((n, 1, h, w), dtype=odt, device=self.device)
+        out_depth = torch.empty((n, 1, h, w), dtype=torch.float32, device=self.device) if return_depth else None
+        out_flow = torch.empty((n, 2, h, w), dtype=torch.float32, device=self.device) if return_flow else None
+        flag = torch.zeros(1, dtype=torch.int32, device=self.device) if check_range else None
+        ws = self._get_workspace(n, h, w, flags)
+        with torch.cuda.device(self.device):
+            rc = self._lib.tcw_forward_warp(self._context(), _ptr(frames_d), _ptr(mask1_d), _ptr(depths_d),
+                                            _ptr(si_d), _ptr(M_d), n, n_src, h, w, flags,
+                                            _ptr(out_frame), _ptr(out_mask), _ptr(out_depth), _ptr(out_flow),
+                                            _ptr(flag), _ptr(ws), ws.numel(), self._stream())
+        _lib.check(rc, "tcw_forward_warp")
+        if check_range:
+            # the reference asserts -1.1 <= warped <= 1.1 before clipping (models/utils.py:580-581)
+            assert int(flag.item()) == 0
+        return out_frame, out_mask, out_depth, out_flow
+
+    def forward_warp_host(self, frames, depths, M, src_index=None, mask1=None, per_frame_max: bool = True,
+                          mask: bool = False, outputs=None):
+        """Host-buffer entry (``tcw_forward_warp_host``): CPU float32 tensors in (ideally pinned),
+        CPU tensors out; uploads, kernels and downloads are pipelined inside the C library.
+        ``M`` is the prepared (n,30) matrix block.  ``outputs`` may carry preallocated pinned
+        (frame, mask, depth, flow) tensors.  Returns (frame, mask, depth, flow, range_flag)."""
+        n_src, _, h, w = frames.shape
+        n = M.shape[0]
+        odt = torch.float64 if mask else torch.float32
+        if outputs is None:
+            outputs = (torch.empty((n, 3, h, w), dtype=odt), torch.empty((n, 1, h, w), dtype=odt),
+                       torch.empty((n, 1, h, w), dtype=torch.float32), torch.empty((n, 2, h, w), dtype=torch.float32))
+        of, om, od, ofl = outputs
+        for t in (frames, depths, M):
+            assert t.device.type == "cpu" and t.dtype == torch.float32 and t.is_contiguous()
+        si = None if src_index is None else src_index.to(torch.int32).contiguous()
+        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0)
+        flag = ctypes.c_int(0)
+        rc = self._lib.tcw_forward_warp_host(self._context(), _ptr(frames), _ptr(mask1), _ptr(depths), _ptr(si),
+                                             _ptr(M), n, n_src, h, w, flags, _ptr(of), _ptr(om), _ptr(od), _ptr(ofl),
+                                             ctypes.byref(flag))
+        _lib.check(rc, "tcw_forward_warp_host")
+        return of, om, od, ofl, flag.value
+
+    # ------------------------------------------------------------------ reference API
+    def forward_warp(
+        self,
+        frame1: torch.Tensor,
+        mask1: Optional[torch.Tensor],
+        depth1: torch.Tensor,
+        transformation1: torch.Tensor,
+        transformation2: torch.Tensor,
+        intrinsic1: torch.Tensor,
+        intrinsic2: Optional[torch.Tensor],
+        mask=False,
+        twice=False,
+    ) -> Tuple[torch.Tensor, torch.Tensor, torch.Tensor, torch.Tensor]:
+        """Drop-in for reference models/utils.py:220-347 (same arguments, shapes and returns).
+
+        frame1 (b,3,h,w) in [-1,1]; mask1 (b,1,h,w)|None; depth1 (b,1,h,w); transformation1/2
+        (b,4,4); intrinsic1/2 (b,3,3).  Returns (warped_frame2, mask2, warped_depth2, flow12), or
+        the twice-warped triple and ``None`` when ``twice=True``.
+        """
+        if self.resolution is not None:
+            assert frame1.shape[2:4] == self.resolution
+        b, c, h, w = frame1.shape
+        assert frame1.shape == (b, 3, h, w)
+        assert mask1 is None or mask1.shape == (b, 1, h, w)
+        assert depth1.shape == (b, 1, h, w)
+        assert transformation1.shape == (b, 4, 4)
+        assert transformation2.shape == (b, 4, 4)
+        assert intrinsic1.shape == (b, 3, 3)
+        assert intrinsic2 is None or intrinsic2.shape == (b, 3, 3)
+        if mask and b != 1:
+            # the reference's clean_points only works for b == 1 (models/utils.py:595-597)
+            raise RuntimeError("forward_warp(mask=True) requires batch size 1, as in the reference")
+
+        if not twice:
+            # one call with b images: the soft-z max is over the whole call (models/utils.py:492)
+            return self.forward_warp_batch(frame1, depth1, transformation1, transformation2, intrinsic1,
+                                           intrinsic2, mask1=mask1, per_frame_max=False, mask=mask)
+
+        # twice=True (models/utils.py:296-347): forward splat, then splat back along the warped flow
+        frame1_d, depth1_d = self._dev(frame1), self._dev(depth1)
+        mask1_d = self._dev(mask1) if mask1 is not None else torch.ones((b, 1, h, w), device=self.device)
+        warped_frame2, mask2, warped_depth2, flow12 = self.forward_warp_batch(
+            frame1_d, depth1_d, transformation1, transformation2, intrinsic1, intrinsic2,
+            mask1=mask1, per_frame_max=False, mask=False)
+        trans_depth1 = self.compute_transformed_points(
+            depth1_d, transformation1, transformation2, intrinsic1, intrinsic2)[:, :, :, 2, 0].contiguous()
+        if mask:
+            warped_frame2, mask2 = self.clean_points(warped_frame2, mask2)
+            warped_depth2, _ = self.clean_points(warped_depth2, mask2)
+        warped_flow, _ = self.bilinear_splatting(flow12, mask1_d, trans_depth1, flow12, None, is_image=False)
+        twice_warped_frame1, twice_warped_mask1 = self.bilinear_splatting(
+            warped_frame2, mask2, warped_depth2.squeeze(1), -warped_flow, None, is_image=True)
+        twice_warped_depth1, _ = self.bilinear_splatting(
+            warped_depth2, mask2, warped_depth2.squeeze(1), -warped_flow, None, is_image=False)
+        if mask:
+            twice_warped_frame1, twice_warped_mask1 = self.clean_points(twice_warped_frame1, twice_warped_mask1)
+            twice_warped_depth1, _ = self.clean_points(twice_warped_depth1, twice_warped_mask1)
+        return twice_warped_frame1, twice_warped_mask1, twice_warped_depth1, None
+
+    def compute_transformed_points(
+        self,
+        depth1: torch.Tensor,
+        transformation1: torch.Tensor,
+        transformation2: torch.Tensor,
+        intrinsic1: torch.Tensor,
+        intrinsic2: Optional[torch.Tensor],
+    ):
+        """Drop-in for models/utils.py:350-420: (b,1,h,w) depth -> (b,h,w,3,1) projected points
+        (all three components 1000 where the transformed point is behind the camera)."""
+        if self.resolution is not None:
+            assert depth1.shape[2:4] == self.resolution
+        b, _, h, w = depth1.shape
+        M_d = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2).to(self.device)
+        depth_d = self._dev(depth1)
+        out = torch.empty((b, h, w, 3), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = self._lib.tcw_project(self._context(), _ptr(depth_d), None, _ptr(M_d), b, b, h, w,
+                                       _ptr(out), self._stream())
+        _lib.check(rc, "tcw_project")
+        return out.unsqueeze(-1)
+
+    def bilinear_splatting(
+        self,
+        frame1: torch.Tensor,
+        mask1: Optional[torch.Tensor],
+        depth1: torch.Tensor,
+        flow12: torch.Tensor,
+        flow12_mask: Optional[torch.Tensor],
+        is_image: bool = False,
+    ) -> Tuple[torch.Tensor, torch.Tensor]:
+        """Drop-in for models/utils.py:422-583.  frame1 (b,c,h,w), c in 1..4; mask1 (b,1,h,w)|None;
+        depth1 (b,h,w) (as the reference actually passes it; (b,1,h,w) is accepted too);
+        flow12 (b,2,h,w); flow12_mask (b,1,h,w)|None.  Returns (warped (b,c,h,w), mask (b,1,h,w))."""
+        if self.resolution is not None:
+            assert frame1.shape[2:4] == self.resolution
+        b, c, h, w = frame1.shape
+        assert flow12.shape == (b, 2, h, w)
+        assert depth1.numel() == b * h * w
+        odt = torch.promote_types(frame1.dtype, torch.float32) if frame1.dtype == torch.float64 else torch.float32
+        frame_d, flow_d = self._dev(frame1), self._dev(flow12)
+        depth_d = self._dev(depth1.reshape(b, h, w))
+        mask1_d, fmask_d = self._dev(mask1), self._dev(flow12_mask)
+        flags = _lib.TCW_IS_IMAGE if is_image else 0
+        out = torch.empty((b, c, h, w), dtype=torch.float32, device=self.device)
+        out_mask = torch.empty((b, 1, h, w), dtype=torch.float32, device=self.device)
+        flag = torch.zeros(1, dtype=torch.int32, device=self.device)
+        need = ctypes.c_size_t(0)
+        _lib.check(self._lib.tcw_workspace_bytes(self._context(), b, h, w, flags, ctypes.byref(need)),
+                   "tcw_workspace_bytes")
+        ws = self._get_workspace(b, h, w, flags)
+        with torch.cuda.device(self.device):
+            rc = self._lib.tcw_splat(self._context(), _ptr(frame_d), _ptr(mask1_d), _ptr(depth_d), _ptr(flow_d),
+                                     _ptr(fmask_d), b, c, h, w, flags, _ptr(out), _ptr(out_mask), _ptr(flag),
+                                     _ptr(ws), ws.numel(), self._stream())
+        _lib.check(rc, "tcw_splat")
+        if is_image:
+            assert int(flag.item()) == 0       # models/utils.py:580-581
+        if odt == torch.float64:               # float64 inputs (after clean_points) stay float64 in the reference
+            out, out_mask = out.double(), out_mask.double()
+        return out, out_mask
+
+    def clean_points(self, warped_frame2, mask2):
+        """Drop-in for models/utils.py:585-626: removes a 2-pixel rim around every hole (5x5 dilation
+        of the hole mask).  b must be 1; outputs are float64 like the reference's."""
+        if warped_frame2.shape[0] != 1:
+            raise RuntimeError("clean_points requires batch size 1, as in the reference")
+        _, c, h, w = warped_frame2.shape
+        frame_d, mask_d = self._dev(warped_frame2), self._dev(mask2)
+        out = torch.empty((1, c, h, w), dtype=torch.float64, device=self.device)
+        out_mask = torch.empty((1, 1, h, w), dtype=torch.float64, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = self._lib.tcw_clean_points(self._context(), _ptr(frame_d), _ptr(mask_d), c, h, w,
+                                            _ptr(out), _ptr(out_mask), self._stream())
+        _lib.check(rc, "tcw_clean_points")
+        return out, out_mask
+
+    @staticmethod
+    def create_grid(b, h, w):
+        """models/utils.py:628-636: (b,2,h,w) int64 pixel grid, channel 0 = x, channel 1 = y."""
+        ys, xs = torch.meshgrid(torch.arange(0, h), torch.arange(0, w), indexing="ij")
+        return torch.stack([xs, ys], dim=0)[None].repeat([b, 1, 1, 1])
+
+    @staticmethod
+    def read_image(path: Path) -> torch.Tensor:
+        """models/utils.py:638-641 (skimage.io.imread there; PIL here — same RGB uint8 array)."""
+        import PIL.Image
+        return numpy.array(PIL.Image.open(path.as_posix()))
+
+    @staticmethod
+    def read_depth(path: Path) -> torch.Tensor:
+        """models/utils.py:643-654: .png / .npy / .npz('depth')."""
+        if path.suffix == '.png':
+            import PIL.Image
+            depth = numpy.array(PIL.Image.open(path.as_posix()))
+        elif path.suffix == '.npy':
+            depth = numpy.load(path.as_posix())
+        elif path.suffix == '.npz':
+            with numpy.load(path.as_posix()) as depth_data:
+                depth = depth_data['depth']
+        else:
+            raise RuntimeError(f'Unknown depth format: {path.suffix}')
+        return depth
+
+    @staticmethod
+    def camera_intrinsic_transform(capture_width=1920, capture_height=1080, patch_start_point: tuple = (0, 0)):
+        """models/utils.py:656-666: 4x4 intrinsics, f=2100, principal point at the (cropped) centre."""
+        start_y, start_x = patch_start_point
+        k = numpy.eye(4)
+        k[0, 0] = k[1, 1] = 2100
+        k[0, 2] = capture_width / 2.0 - start_x
+        k[1, 2] = capture_height / 2.0 - start_y
+        return k
+
+    @staticmethod
+    def get_device(device: str):
+        """'gpuN' (reference spelling), 'cuda' or 'cuda:N' -> torch.device('cuda', N).
+
+        Deviation from models/utils.py:668-682, which silently falls back to the CPU for anything
+        but 'gpuN' (and so runs every shipped caller on the CPU): this implementation has no CPU
+        path, so 'cpu' — or a CUDA request without a GPU — raises instead of falling back."""
+        if isinstance(device, torch.device):
+            device = str(device)
+        if device.startswith('gpu'):
+            dev = torch.device(f'cuda:{int(device[3:])}')
+        elif device.startswith('cuda'):
+            dev = torch.device(device if ':' in device else 'cuda:0')
+        else:
+            raise ValueError(f"Warper device {device!r}: this implementation is CUDA-only (no CPU fallback)")
+        return dev
