@@ -1,0 +1,213 @@
+"""GPU: parity of the CUDA path (through the C ABI) with the reference-pinned goldens and the oracle."""
+import numpy as np
+import pytest
+import torch
+
+import oracle
+from _util import assert_colour_close, assert_depth_close, bit_equal, warp_case_names
+from trajectorycrafter_b200 import Warper, prepare_matrices
+from trajectorycrafter_b200.workloads import ORBIT_PRESETS, orbit_units, ring_cameras, synthetic_clip
+
+pytestmark = pytest.mark.gpu
+
+
+@pytest.fixture(scope="module")
+def warper():
+    assert torch.cuda.is_available(), "these tests need the B200"
+    return Warper(device="cuda:0")
+
+
+def T(a):
+    return None if a is None else torch.from_numpy(np.ascontiguousarray(a))
+
+
+def npy(t):
+    return None if t is None else t.detach().cpu().numpy()
+
+
+def check_against(got, ref_frame, ref_mask, ref_depth, ref_flow, tol=1e-5):
+    gf, gm, gd, gfl = [npy(t) for t in got]
+    assert bit_equal(gm.astype(ref_mask.dtype), ref_mask), "validity mask must be bit-exact"
+    if ref_flow is not None:
+        assert bit_equal(gfl, ref_flow), "flow12 must be bit-exact"
+    e1 = assert_colour_close(gf, ref_frame, tol=tol)
+    e2 = assert_depth_close(gd, ref_depth, ref_mask, rtol=tol)
+    return e1, e2
+
+
+@pytest.mark.parametrize("name", warp_case_names(twice=False, clean=False))
+def test_golden_forward_warp(warper, golden, name):
+    """CUDA vs outputs of the unmodified reference (fixtures), on the stored matrix block."""
+    c = golden[name]
+    b = c["frame"].shape[0]
+    got = warper.forward_warp_matrices(T(c["frame"]), T(c["depth"]), T(c["M"]), mask1=T(c.get("mask1")),
+                                       per_frame_max=(b == 1))
+    check_against(got, c["out_frame"], c["out_mask"], c["out_depth"], c["out_flow"])
+
+
+@pytest.mark.parametrize("name", warp_case_names(twice=False, clean=False))
+def test_dropin_signature_vs_oracle(warper, golden, name):
+    """The reference-signature call (host computes the matrix block with torch CPU here)."""
+    c = golden[name]
+    args = [T(c["frame"]), T(c.get("mask1")), T(c["depth"]), T(c["T1"]), T(c["T2"]), T(c["K1"]), T(c.get("K2"))]
+    got = warper.forward_warp(*args)
+    M = prepare_matrices(args[3], args[4], args[5], args[6])
+    ref = oracle.forward_warp(c["frame"], c.get("mask1"), c["depth"], M, per_unit_max=False)
+    check_against(got, ref[0], ref[1], ref[2], ref[3])
+    assert got[0].shape == c["out_frame"].shape and got[3].shape == c["out_flow"].shape
+
+
+@pytest.mark.parametrize("name", warp_case_names(twice=False))
+def test_golden_projection_bit_exact(warper, golden, name):
+    c = golden[name]
+    M = T(c["M"]).cuda()
+    d = T(c["depth"]).cuda()
+    b, _, h, w = d.shape
+    out = torch.empty((b, h, w, 3), device="cuda")
+    rc = warper._lib.tcw_project(warper._context(), d.data_ptr(), None, M.data_ptr(), b, b, h, w, out.data_ptr(),
+                                 torch.cuda.current_stream().cuda_stream)
+    assert rc == 0
+    assert bit_equal(npy(out), c["points"])
+    pts = warper.compute_transformed_points(T(c["depth"]), T(c["T1"]), T(c["T2"]), T(c["K1"]), T(c.get("K2")))
+    assert pts.shape == (b, h, w, 3, 1)
+
+
+@pytest.mark.parametrize("name", warp_case_names(twice=False, clean=True))
+def test_golden_mask_true(warper, golden, name):
+    """mask=True: fused clean_points, float64 outputs, cleaned pixels exactly -1 (H7)."""
+    c = golden[name]
+    got = warper.forward_warp_matrices(T(c["frame"]), T(c["depth"]), T(c["M"]), mask=True)
+    assert got[0].dtype == torch.float64 and got[1].dtype == torch.float64
+    gf, gm, gd, gfl = [npy(t) for t in got]
+    assert bit_equal(gm, c["out_mask"])
+    assert bit_equal(gfl, c["out_flow"])
+    assert np.all(gf[np.broadcast_to(gm == 0, gf.shape)] == -1.0)
+    assert_colour_close(gf, c["out_frame"])
+    with pytest.raises(RuntimeError):   # b>1 with mask=True fails in the reference too
+        warper.forward_warp(torch.zeros(2, 3, 8, 8), None, torch.ones(2, 1, 8, 8), torch.eye(4).repeat(2, 1, 1),
+                            torch.eye(4).repeat(2, 1, 1), torch.eye(3).repeat(2, 1, 1), None, mask=True)
+
+
+def test_golden_standalone_ops(warper, golden):
+    c = golden["splat_c2"]
+    out, om = warper.bilinear_splatting(T(c["frame"]), T(c["mask1"]), T(c["depth"]), T(c["frame"]), None, is_image=False)
+    assert bit_equal(npy(om), c["out_mask"])
+    assert_colour_close(npy(out), c["out"])
+    c = golden["splat_c3_img"]
+    out, om = warper.bilinear_splatting(T(c["frame"]), None, T(c["depth"]), T(c["flow"]), T(c["flow_mask"]), is_image=True)
+    assert bit_equal(npy(om), c["out_mask"])
+    assert_colour_close(npy(out), c["out"])
+    for name in ("clean_c3", "clean_c1"):
+        c = golden[name]
+        cf, cm = warper.clean_points(T(c["frame"]), T(c["mask2"]))
+        assert bit_equal(npy(cm), c["out_mask"]) and bit_equal(npy(cf), c["out"])
+
+
+def test_golden_twice(warper, golden):
+    c = golden["twice_phi12"]
+    got = warper.forward_warp(T(c["frame"]), None, T(c["depth"]), T(c["T1"]), T(c["T2"]), T(c["K1"]), None, twice=True)
+    assert got[3] is None
+    assert bit_equal(npy(got[1]), c["out_mask"])
+    assert_colour_close(npy(got[0]), c["out_frame"], tol=2e-5)
+    assert_depth_close(npy(got[2]), c["out_depth"], c["out_mask"], rtol=2e-5)
+
+
+def test_shape_asserts_like_the_reference(warper):
+    f, d = torch.zeros(1, 3, 8, 8), torch.ones(1, 1, 8, 8)
+    e4, e3 = torch.eye(4)[None], torch.eye(3)[None]
+    with pytest.raises(AssertionError):
+        warper.forward_warp(f, None, torch.ones(1, 1, 8, 9), e4, e4, e3, None)
+    with pytest.raises(AssertionError):
+        warper.forward_warp(f, torch.ones(1, 2, 8, 8), d, e4, e4, e3, None)
+    with pytest.raises(AssertionError):
+        Warper(resolution=(4, 4), device="gpu0").forward_warp(f, None, d, e4, e4, e3, None)
+    # range assert: colours far outside [-1,1] trip the reference's check (models/utils.py:580-581)
+    with pytest.raises(AssertionError):
+        warper.forward_warp(f + 5.0, None, d, e4, e4, e3, None)
+
+
+@pytest.fixture(scope="module")
+def clip():
+    return synthetic_clip(49, 384, 672, seed=1234)
+
+
+def test_full_size_vs_oracle_orbits(warper, clip):
+    """BASELINE config 2 at full resolution on a subset of units: frames {0,24,48} x 8 orbit presets."""
+    frames, depths = clip
+    T1, T2, K, src = orbit_units(depths, 384, 672)
+    pick = torch.cat([torch.arange(8) + 8 * f for f in (0, 24, 48)])
+    M = prepare_matrices(T1[pick], T2[pick], K[pick])
+    got = warper.forward_warp_matrices(frames, depths, M, src_index=src[pick])
+    ref = oracle.forward_warp(frames, None, depths, M, src_index=src[pick].numpy(), per_unit_max=True)
+    e = check_against(got, ref[0], ref[1], ref[2], ref[3])
+    print("config2 subset: colour max|d| %.2e depth max rel %.2e" % e)
+
+
+def test_full_size_per_unit_equals_single_calls(warper, clip):
+    """Batched per-frame-max submission == the reference's one-call-per-frame loop (demo.py:77-90)."""
+    frames, depths = clip
+    T1, T2, K, src = orbit_units(depths, 384, 672, presets=[ORBIT_PRESETS[1]])
+    batch = warper.forward_warp_batch(frames[:6], depths[:6], T1[:6], T2[:6], K[:6])
+    for i in (0, 3, 5):
+        one = warper.forward_warp(frames[i:i + 1], None, depths[i:i + 1], T1[i:i + 1], T2[i:i + 1], K[i:i + 1], None)
+        assert torch.equal(one[1], batch[1][i:i + 1]) and torch.equal(one[3], batch[3][i:i + 1])
+        assert_colour_close(npy(one[0]), npy(batch[0][i:i + 1]))
+
+
+def test_1080p_stress_vs_oracle(warper):
+    """BASELINE config 3: 1080p, (0,30,0.3) trajectory + contention stress (25% behind the camera)."""
+    frames, depths = synthetic_clip(2, 1080, 1920, seed=5)
+    T1, T2, K, src = orbit_units(depths, 1080, 1920, d_r=0.3, presets=[(0, 30)])
+    K[:] = torch.tensor([[1500.0, 0, 960], [0, 1500.0, 540], [0, 0, 1]])
+    depths = depths.clone()
+    depths[1, :, :, :480] = 0.0           # zero depth: with the 30 degree orbit these stay in front ...
+    M = prepare_matrices(T1, T2, K)
+    M[1, 9:21] = prepare_matrices(T1[:1], torch.diag(torch.tensor([-1.0, 1, -1, 1]))[None] @ T2[:1], K[:1])[0, 9:21]
+    got = warper.forward_warp_matrices(frames, depths, M)   # ... unit 1 looks backwards: everything is behind
+    ref = oracle.forward_warp(frames, None, depths, M, per_unit_max=True)
+    check_against(got, ref[0], ref[1], ref[2], ref[3])
+
+
+def test_ring_cameras_vs_oracle(warper, clip):
+    """BASELINE config 4 style: general extrinsics, K_t != K_s, 16 targets x 2 frames."""
+    frames, depths = clip
+    ext, ks = ring_cameras(16)
+    src = torch.tensor([0, 30], dtype=torch.int32).repeat_interleave(16)
+    T1 = ext[0:1].repeat(32, 1, 1)
+    T2 = ext.repeat(2, 1, 1)
+    M = prepare_matrices(T1, T2, ks[0:1].repeat(32, 1, 1), ks.repeat(2, 1, 1))
+    d = (depths / depths.max() * 10.0 + 2.0)
+    got = warper.forward_warp_matrices(frames, d, M, src_index=src)
+    ref = oracle.forward_warp(frames, None, d, M, src_index=src.numpy(), per_unit_max=True)
+    check_against(got, ref[0], ref[1], ref[2], ref[3])
+
+
+def test_host_buffer_entry_matches_device_entry(warper, clip):
+    frames, depths = clip
+    T1, T2, K, src = orbit_units(depths[:5], 384, 672, presets=ORBIT_PRESETS[:3])
+    M = prepare_matrices(T1, T2, K)
+    dev = warper.forward_warp_matrices(frames[:5], depths[:5], M, src_index=src)
+    host = warper.forward_warp_host(frames[:5].contiguous(), depths[:5].contiguous(), M, src_index=src)
+    assert host[4] == 0
+    assert torch.equal(host[1], dev[1].cpu()) and torch.equal(host[3], dev[3].cpu())
+    assert_colour_close(host[0].numpy(), npy(dev[0]))
+    assert_depth_close(host[2].numpy(), npy(dev[2]), npy(dev[1]))
+
+
+def test_size_independent_properties(warper, clip):
+    """Full-size properties that need no oracle: identity round trip, hole/mask consistency,
+    colour-channel permutation equivariance, and mask == (warped depth > 0)."""
+    frames, depths = clip
+    n = 4
+    eye4, K = torch.eye(4).repeat(n, 1, 1), torch.tensor([[328.125, 0, 336], [0, 333.3333, 192], [0, 0, 1]]).repeat(n, 1, 1)
+    f, m, d, fl = warper.forward_warp_batch(frames[:n], depths[:n], eye4, eye4, K)
+    assert float(m.min()) == 1.0 and float(fl.abs().max()) < 1e-3
+    assert float((f.cpu() - frames[:n]).abs().max()) < 2e-3          # identity warp reproduces the frame
+    T1, T2, K, src = orbit_units(depths[:n], 384, 672, presets=[(0, -45)])
+    f, m, d, fl = warper.forward_warp_batch(frames[:n], depths[:n], T1, T2, K)
+    assert torch.equal(m > 0, d > 0)
+    assert torch.all(f[(m == 0).expand_as(f)] == -1.0) and float(f.abs().max()) <= 1.0
+    perm = [2, 0, 1]
+    f2, m2, _, fl2 = warper.forward_warp_batch(frames[:n][:, perm].contiguous(), depths[:n], T1, T2, K)
+    assert torch.equal(m, m2) and torch.equal(fl, fl2)
+    assert_colour_close(npy(f2), npy(f[:, perm]))

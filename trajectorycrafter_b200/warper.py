@@ -96,17 +96,33 @@ class Warper:
         Returns (warped (n,3,h,w), mask (n,1,h,w), depth (n,1,h,w)|None, flow12 (n,2,h,w)|None);
         warped/mask are float64 when ``mask=True`` (reference quirk, models/utils.py:618-626).
         """
-        n_src, c, h, w = frames.shape
         n = transformation1.shape[0]
-        assert c == 3 and depths.shape == (n_src, 1, h, w)
+        M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
+        assert M.shape[0] == n
+        return self.forward_warp_matrices(frames, depths, M, mask1=mask1, src_index=src_index,
+                                          per_frame_max=per_frame_max, mask=mask, return_depth=return_depth,
+                                          return_flow=return_flow, check_range=check_range,
+                                          deterministic=deterministic)
+
+    def forward_warp_matrices(self, frames: torch.Tensor, depths: torch.Tensor, M: torch.Tensor,
+                              mask1: Optional[torch.Tensor] = None, src_index: Optional[torch.Tensor] = None,
+                              per_frame_max: bool = True, mask: bool = False,
+                              return_depth: bool = True, return_flow: bool = True, check_range: bool = True,
+                              deterministic: bool = False):
+        """``forward_warp_batch`` on an already prepared (n_units,30) matrix block
+        (``prepare_matrices``): [K1^-1 | rows 0..2 of T2*T1^-1 | K2] per unit."""
+        n_src, c, h, w = frames.shape
+        n = M.shape[0]
+        assert c == 3 and depths.shape == (n_src, 1, h, w) and M.shape == (n, 30)
         if mask1 is not None:
             assert mask1.shape == (n_src, 1, h, w)
         if src_index is None:
             assert n == n_src, "src_index is required when the number of poses differs from the number of frames"
-        M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
-        assert M.shape[0] == n
+        else:
+            assert src_index.shape == (n,)
+            assert int(src_index.min()) >= 0 and int(src_index.max()) < n_src
         frames_d, depths_d, mask1_d = self._dev(frames), self._dev(depths), self._dev(mask1)
-        M_d = M.to(self.device, non_blocking=True)
+        M_d = M.to(self.device, torch.float32, non_blocking=True).contiguous()
         si_d = None if src_index is None else src_index.to(self.device, torch.int32).contiguous()
         flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) \
             | (_lib.TCW_DETERMINISTIC if deterministic else 0)
