@@ -1,0 +1,323 @@
+#!/usr/bin/env python
+"""bench.py — headline benchmark of the forward re-rendering path (BASELINE.json).
+
+    python bench.py [--gpus N] [--steps K] [--warmup W] [--impl ours|reference]
+
+Metric: warped Mpix/s on BASELINE config 2 — a synthetic RGB+depth clip of 49 frames at 384x672
+warped along the 8 inference_orbits.py orbit presets = 392 (frame, pose) units = 101.2 Mpix per
+step per GPU.  One "step" is one pass of the hot path over that batch.  Multi-GPU is weak scaling:
+every rank warps its own clip's 392 units, no data-path collective in the timed step (units are
+independent); `value` = units of all ranks / max-over-ranks device time.  The one exchange the
+pipeline has — gathering the warped condition video on the denoiser's rank — is timed separately
+and reported under "gather".
+
+One JSON line on stdout (rank 0).  See the driver contract in the task statement for the keys.
+"""
+import argparse
+import json
+import os
+import statistics
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+if ROOT not in sys.path:
+    sys.path.insert(0, ROOT)
+
+ALGO_BYTES_PER_PX = 44.0          # read RGB 12 + depth 4, write colour 12 + mask 4 + depth 4 + flow 8
+N_FRAMES, H, W = 49, 384, 672
+
+
+def load_peaks():
+    path = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(path):
+        with open(path) as fh:
+            return float(json.load(fh)["hbm_gbs"]), "measured (MEASURED_PEAKS.json hbm_gbs)"
+    return 6650.0, "fallback (B200_PROFILING.md 6.65 TB/s)"
+
+
+class ClockSampler:
+    """Samples SM clock and throttle reasons of one GPU during the timed region (NVML, ~5 ms period)."""
+
+    def __init__(self, index):
+        self.index, self.samples, self.reasons, self.max_mhz = index, [], set(), None
+        self._stop = threading.Event()
+        self._thread = None
+        try:
+            import pynvml
+            pynvml.nvmlInit()
+            self.nv = pynvml
+            self.handle = pynvml.nvmlDeviceGetHandleByIndex(index)
+            self.max_mhz = pynvml.nvmlDeviceGetMaxClockInfo(self.handle, pynvml.NVML_CLOCK_SM)
+        except Exception:
+            self.nv = None
+
+    def _loop(self):
+        nv = self.nv
+        names = {
+            "hw_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwSlowdown", 0x8),
+            "hw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonHwThermalSlowdown", 0x40),
+            "sw_thermal_slowdown": getattr(nv, "nvmlClocksThrottleReasonSwThermalSlowdown", 0x20),
+            "sw_power_cap": getattr(nv, "nvmlClocksThrottleReasonSwPowerCap", 0x4),
+        }
+        while not self._stop.is_set():
+            try:
+                self.samples.append(nv.nvmlDeviceGetClockInfo(self.handle, nv.NVML_CLOCK_SM))
+                mask = nv.nvmlDeviceGetCurrentClocksThrottleReasons(self.handle)
+                for k, bit in names.items():
+                    if mask & bit:
+                        self.reasons.add(k)
+            except Exception:
+                pass
+            time.sleep(0.005)
+
+    def start(self):
+        if self.nv is not None:
+            self._thread = threading.Thread(target=self._loop, daemon=True)
+            self._thread.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._thread is not None:
+            self._thread.join(1.0)
+        if not self.samples:
+            return {"sm_mhz": None, "sm_max_mhz": self.max_mhz, "reasons": [], "samples": 0}
+        return {"sm_mhz": statistics.median(self.samples), "sm_max_mhz": self.max_mhz,
+                "reasons": sorted(self.reasons), "samples": len(self.samples)}
+
+
+def build_workload(seed):
+    import torch
+    from trajectorycrafter_b200 import prepare_matrices
+    from trajectorycrafter_b200.workloads import orbit_units, synthetic_clip
+    frames, depths = synthetic_clip(N_FRAMES, H, W, seed=seed)
+    T1, T2, K, src = orbit_units(depths, H, W)
+    M = prepare_matrices(T1, T2, K)
+    return frames, depths, M, src.to(torch.int32)
+
+
+def oracle_throughput(frames, depths, M, src, unit_ids, threads):
+    """Times the CPU oracle (oracle/warp_oracle.c, the port of the reference's path) on `unit_ids`,
+    one unit per task over `threads` host threads.  Returns (Mpix/s, seconds)."""
+    from concurrent.futures import ThreadPoolExecutor
+    import oracle
+    src_np = src.numpy()
+
+    def one(u):
+        oracle.forward_warp(frames, None, depths, M[u:u + 1], src_index=src_np[u:u + 1], per_unit_max=True)
+
+    t0 = time.perf_counter()
+    with ThreadPoolExecutor(threads) as ex:
+        list(ex.map(one, unit_ids))
+    dt = time.perf_counter() - t0
+    return len(unit_ids) * H * W / dt / 1e6, dt
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation of the path, timed on the host cores.
+    The reference is pure Python/torch and cannot travel to the GPU box, so this is the oracle port
+    (kind "port"), threaded over units with every host core."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    import oracle
+    oracle.build()
+    frames, depths, M, src = build_workload(1234)
+    threads = os.cpu_count() or 1
+    # bounded sample per step: every 6th frame x 8 presets = 72 of the 392 units
+    unit_ids = [f * 8 + p for f in range(0, N_FRAMES, 6) for p in range(8)]
+    for _ in range(max(1, min(args.warmup, 2))):
+        oracle_throughput(frames, depths, M, src, unit_ids[:threads], threads)
+    t0 = time.perf_counter()
+    for _ in range(args.steps):
+        oracle_throughput(frames, depths, M, src, unit_ids, threads)
+    dt = (time.perf_counter() - t0) / args.steps
+    value = len(unit_ids) * H * W / dt / 1e6
+    sample = f"{len(unit_ids)} of 392 units per step (every 6th frame x 8 orbit presets), {threads} threads"
+    line = {
+        "impl": "reference", "metric": "warped_mpix_per_s", "value": value, "unit": "Mpix/s",
+        "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
+        "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+        "config": workload_config(),
+        "cpu_baseline": {"value": value, "unit": "Mpix/s", "cores": threads, "kind": "port", "sample": sample},
+        "e2e": {"value": value, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def workload_config():
+    return {"workload": "config2: synthetic RGB+depth 49x384x672 x 8 inference_orbits.py orbit presets "
+                        "(392 frame/pose units = 101.2 Mpix per step per GPU), per-frame soft-z max, mask1=None",
+            "units_per_step_per_gpu": N_FRAMES * 8, "frames": N_FRAMES, "h": H, "w": W,
+            "l2": "per-step inputs+outputs are 3.0 GB >> 126 MB L2, so no L2 flush between steps",
+            "sharding": "units are independent: each rank warps its own 392 units, no collective in the step"}
+
+
+def run_ours(args):
+    import torch
+    import torch.distributed as dist
+    from trajectorycrafter_b200 import Warper
+
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    rank = int(os.environ.get("RANK", "0"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: this path has no CPU fallback")
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+        dist.init_process_group("nccl", device_id=dev)
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def max_over_ranks(v):
+        if world == 1:
+            return v
+        t = torch.tensor([v], dtype=torch.float64, device=dev)
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    frames, depths, M, src = build_workload(1234 + rank)
+    n_units = M.shape[0]
+    px_per_step = n_units * H * W
+    warper = Warper(device=f"cuda:{local}")
+    frames_d, depths_d = frames.to(dev), depths.to(dev)
+    out = (torch.empty((n_units, 3, H, W), device=dev), torch.empty((n_units, 1, H, W), device=dev),
+           torch.empty((n_units, 1, H, W), device=dev), torch.empty((n_units, 2, H, W), device=dev))
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+
+    def step():
+        warper.forward_warp_matrices(frames_d, depths_d, M, src_index=src, per_frame_max=True,
+                                     check_range=flag, out=out)
+
+    for _ in range(max(3, args.warmup)):
+        step()
+    barrier()
+    # ---- timed region: K steps, device-timed on the launching (current) stream
+    sampler = ClockSampler(local)
+    warper.profile(True)
+    launches0 = warper.launch_count()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    sampler.start()
+    ev0.record()
+    for _ in range(args.steps):
+        step()
+    ev1.record()
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    barrier()
+    ms_local = ev0.elapsed_time(ev1) / args.steps
+    launches = warper.launch_count() - launches0
+    prof = warper.profile_read()
+    warper.profile(False)
+    assert int(flag.item()) == 0, "range check failed"
+    ms = max_over_ranks(ms_local)
+    value = world * px_per_step / (ms * 1e-3) / 1e6
+
+    # ---- roofline of the dominant kernel (live CUDA-event durations of every launch in the timed region)
+    peak, peak_src = load_peaks()
+    k_ms, k_n, k_units = prof["project_splat"]
+    roofline = None
+    if k_n:
+        achieved = ALGO_BYTES_PER_PX * k_units * H * W / (k_ms * 1e-3) / 1e9
+        total_k_ms = sum(v[0] for v in prof.values())
+        roofline = {"bound": "hbm", "kernel": "k_project_splat_f32", "achieved": achieved, "peak": peak,
+                    "unit": "GB/s", "frac": achieved / peak, "traffic": None,
+                    "peak_source": peak_src, "avg_launch_us": k_ms / k_n * 1e3, "launches": k_n,
+                    "algorithmic_bytes_per_launch": ALGO_BYTES_PER_PX * k_units * H * W / k_n,
+                    "kernel_share_of_step": k_ms / total_k_ms if total_k_ms else None,
+                    "per_kernel_ms_per_step": {k: v[0] / args.steps for k, v in prof.items()},
+                    "step_frac": ALGO_BYTES_PER_PX * px_per_step / (ms_local * 1e-3) / 1e9 / peak}
+
+    # ---- e2e: host buffers through the C-ABI host entry (H2D + kernels + D2H inside the timed region)
+    e2e = None
+    if not args.no_e2e:
+        hf, hd = frames.pin_memory(), depths.pin_memory()
+        houts = (torch.empty((n_units, 3, H, W)).pin_memory(), torch.empty((n_units, 1, H, W)).pin_memory(),
+                 torch.empty((n_units, 1, H, W)).pin_memory(), torch.empty((n_units, 2, H, W)).pin_memory())
+        Mh = M.contiguous()
+        warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=houts)
+        barrier()
+        k_e2e = max(1, min(args.steps, 5))
+        t0 = time.perf_counter()
+        for _ in range(k_e2e):
+            res = warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=houts)
+        dt = (time.perf_counter() - t0) / k_e2e
+        assert res[4] == 0
+        dt = max_over_ranks(dt)
+        e2e = {"value": world * px_per_step / dt / 1e6, "unit": "Mpix/s",
+               "h2d_bytes_per_step": int(hf.numel() * 4 + hd.numel() * 4 + Mh.numel() * 4 + src.numel() * 4),
+               "d2h_bytes_per_step": int(sum(t.numel() * 4 for t in houts) + 4),
+               "ms_per_step": dt * 1e3, "steps": k_e2e,
+               "api": "Warper.forward_warp_host -> tcw_forward_warp_host (pinned host buffers)"}
+        del houts
+
+    # ---- the path's one exchange step: gather colour+mask of one 49-unit trajectory per rank on rank 0
+    gather = None
+    if world > 1:
+        from trajectorycrafter_b200.sharding import gather_condition_video
+        n_g = N_FRAMES
+        col, msk = out[0][:n_g].contiguous(), out[1][:n_g].contiguous()
+        for _ in range(2):
+            gather_condition_video(col, msk, n_g * world, dst=0)
+        barrier()
+        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        g0.record()
+        for _ in range(5):
+            gather_condition_video(col, msk, n_g * world, dst=0)
+        g1.record()
+        torch.cuda.synchronize()
+        g_ms = max_over_ranks(g0.elapsed_time(g1) / 5)
+        wire = n_g * H * W * 13 * (world - 1)
+        gather = {"ms": g_ms, "bytes_into_rank0": wire, "ingress_GBps": wire / (g_ms * 1e-3) / 1e9,
+                  "what": "NCCL gather of colour f32 + mask u8 (13 B/px) of 49 units per rank to rank 0"}
+
+    # ---- CPU baseline (rank 0, N=1 only): the oracle port on the host cores, one full step once
+    cpu_baseline = None
+    if rank == 0 and world == 1 and not args.no_cpu_baseline:
+        import oracle
+        oracle.build()
+        threads = os.cpu_count() or 1
+        v, secs = oracle_throughput(frames, depths, M, src, list(range(n_units)), threads)
+        cpu_baseline = {"value": v, "unit": "Mpix/s", "cores": threads, "kind": "port",
+                        "sample": f"all 392 units of one step, once ({secs:.1f} s wall on {threads} threads)"}
+
+    if rank == 0:
+        line = {
+            "metric": "warped_mpix_per_s", "value": value, "unit": "Mpix/s", "n_gpus": world,
+            "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": workload_config(), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "roofline": roofline, "cpu_baseline": cpu_baseline,
+        }
+        if gather is not None:
+            line["gather"] = gather
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=20)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_ours(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -50,6 +50,15 @@ const char* tcw_last_error(void);
 /* number of kernels this library has launched on behalf of ctx since creation (bench evidence) */
 long long tcw_launch_count(const tcw_ctx* ctx);
 
+/*
+ * Optional per-kernel device timing (CUDA events around every launch, on the launching stream).
+ * tcw_profile_read synchronises on the recorded events, sums them per kernel class
+ * [0]=depth-max pre-pass, [1]=project+splat, [2]=normalise, and resets the log.
+ * ms/launches/units are arrays of 3; units = number of warp units those launches processed.
+ */
+int tcw_profile_enable(tcw_ctx* ctx, int enable);
+int tcw_profile_read(tcw_ctx* ctx, double* ms, long long* launches, double* units);
+
 /* Scratch size needed by tcw_forward_warp / tcw_splat for these shapes (device bytes). */
 int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, int flags, size_t* bytes);
 

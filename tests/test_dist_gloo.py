@@ -1,0 +1,58 @@
+"""CPU, world_size 2 over gloo: unit sharding + the gather of the warped condition video."""
+import os
+import socket
+
+import torch
+import torch.distributed as dist
+import torch.multiprocessing as mp
+
+from trajectorycrafter_b200.sharding import gather_condition_video, shard_bounds
+
+
+def _free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def _worker(rank, world, port, n_units, results):
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        h, w = 6, 10
+        g = torch.Generator().manual_seed(11)
+        colour_all = torch.rand((n_units, 3, h, w), generator=g) * 2 - 1
+        mask_all = (torch.rand((n_units, 1, h, w), generator=g) > 0.4).float()
+        lo, hi = shard_bounds(n_units, world, rank)
+        col, msk = gather_condition_video(colour_all[lo:hi].clone(), mask_all[lo:hi].clone(), n_units, dst=0)
+        if rank == 0:
+            ok = torch.equal(col, colour_all) and torch.equal(msk, mask_all)
+            results.put(("ok" if ok else "mismatch", tuple(col.shape)))
+        else:
+            assert col is None and msk is None
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def _run(n_units):
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker, args=(r, 2, port, n_units, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    status, shape = q.get()
+    assert status == "ok" and shape[0] == n_units
+
+
+def test_gather_even_shards():
+    _run(8)
+
+
+def test_gather_ragged_shards():
+    _run(7)

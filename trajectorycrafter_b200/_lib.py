@@ -22,6 +22,8 @@ SIGNATURES = {
     "tcw_version": (c_int, []),
     "tcw_last_error": (c_char_p, []),
     "tcw_launch_count": (c_longlong, [c_void_p]),
+    "tcw_profile_enable": (c_int, [c_void_p, c_int]),
+    "tcw_profile_read": (c_int, [c_void_p, POINTER(c_double), POINTER(c_longlong), POINTER(c_double)]),
     "tcw_workspace_bytes": (c_int, [c_void_p, c_int, c_int, c_int, c_int, POINTER(c_size_t)]),
     "tcw_forward_warp": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int,
                                  _VP, _VP, _FP, _FP, _IP, _VP, c_size_t, c_void_p]),

@@ -43,7 +43,63 @@ struct tcw_ctx {
     cudaStream_t s_in, s_run, s_out;
     void* pool;
     size_t pool_bytes;
+    // optional per-kernel timing (tcw_profile_*): event pairs around every launch
+    int prof_on;
+    struct ProfRec { int kernel; double units; cudaEvent_t e0, e1; }* prof;
+    int prof_n, prof_cap;
 };
+
+enum { PK_ZMAX = 0, PK_SPLAT = 1, PK_NORMALISE = 2, PK_COUNT = 3 };
+
+static void prof_begin(tcw_ctx* ctx, int kernel, double units, cudaStream_t st) {
+    if (!ctx->prof_on) return;
+    if (ctx->prof_n == ctx->prof_cap) {
+        int cap = ctx->prof_cap ? ctx->prof_cap * 2 : 1024;
+        if (cap > (1 << 17)) { ctx->prof_on = 2; return; }      // cap reached: stop recording
+        auto* p = (tcw_ctx::ProfRec*)realloc(ctx->prof, sizeof(tcw_ctx::ProfRec) * cap);
+        if (!p) return;
+        for (int i = ctx->prof_cap; i < cap; ++i) {
+            cudaEventCreate(&p[i].e0);
+            cudaEventCreate(&p[i].e1);
+        }
+        ctx->prof = p;
+        ctx->prof_cap = cap;
+    }
+    if (ctx->prof_on != 1) return;
+    auto& r = ctx->prof[ctx->prof_n];
+    r.kernel = kernel;
+    r.units = units;
+    cudaEventRecord(r.e0, st);
+}
+static void prof_end(tcw_ctx* ctx, cudaStream_t st) {
+    if (ctx->prof_on != 1) return;
+    cudaEventRecord(ctx->prof[ctx->prof_n].e1, st);
+    ctx->prof_n++;
+}
+
+TCW_API int tcw_profile_enable(tcw_ctx* ctx, int enable) {
+    if (!ctx) return fail(TCW_E_ARG, "tcw_profile_enable: ctx is NULL");
+    ctx->prof_on = enable ? 1 : 0;
+    ctx->prof_n = 0;
+    return TCW_OK;
+}
+
+TCW_API int tcw_profile_read(tcw_ctx* ctx, double* ms, long long* launches, double* units) {
+    if (!ctx || !ms || !launches || !units) return fail(TCW_E_ARG, "tcw_profile_read: NULL argument");
+    for (int k = 0; k < PK_COUNT; ++k) { ms[k] = 0; launches[k] = 0; units[k] = 0; }
+    for (int i = 0; i < ctx->prof_n; ++i) {
+        auto& r = ctx->prof[i];
+        CUDA_TRY(cudaEventSynchronize(r.e1));
+        float t = 0;
+        CUDA_TRY(cudaEventElapsedTime(&t, r.e0, r.e1));
+        ms[r.kernel] += t;
+        launches[r.kernel] += 1;
+        units[r.kernel] += r.units;
+    }
+    ctx->prof_n = 0;
+    if (ctx->prof_on == 2) ctx->prof_on = 1;
+    return TCW_OK;
+}
 
 TCW_API int tcw_version(void) { return TCW_VERSION; }
 TCW_API const char* tcw_last_error(void) { return g_err; }
@@ -73,6 +129,8 @@ TCW_API void tcw_destroy(tcw_ctx* c) {
     cudaGetDevice(&prev);
     cudaSetDevice(c->device);
     if (c->pool) cudaFree(c->pool);
+    for (int i = 0; i < c->prof_cap; ++i) { cudaEventDestroy(c->prof[i].e0); cudaEventDestroy(c->prof[i].e1); }
+    free(c->prof);
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_run) cudaStreamDestroy(c->s_run);
     if (c->s_out) cudaStreamDestroy(c->s_out);
@@ -483,16 +541,22 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         const dim3 grid(tiles_x * tiles_y, nu);
         CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)nu * NCH * hw * sizeof(float), st));
         if (per_unit) {
+            prof_begin(ctx, PK_ZMAX, nu, st);
             k_zmax<<<grid, TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, Lbits, n_units);
+            prof_end(ctx, st);
             LAUNCH_CHECK("k_zmax");
         }
+        prof_begin(ctx, PK_SPLAT, nu, st);
         k_project_splat_f32<<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
                                                           Lbits, per_unit ? -1 : n_units, acc, out_flow);
+        prof_end(ctx, st);
         LAUNCH_CHECK("k_project_splat_f32");
+        prof_begin(ctx, PK_NORMALISE, nu, st);
         if (flags & TCW_CLEAN)
             k_normalise<true><<<grid, TILE_THREADS, 0, st>>>(acc, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
         else
             k_normalise<false><<<grid, TILE_THREADS, 0, st>>>(acc, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
+        prof_end(ctx, st);
         LAUNCH_CHECK("k_normalise");
     }
     return TCW_OK;

@@ -77,6 +77,19 @@ class Warper:
         """Kernels launched by libtcwarp for this Warper so far (bench.py's gpu_launches)."""
         return int(self._lib.tcw_launch_count(self._context()))
 
+    def profile(self, enable: bool) -> None:
+        """Record CUDA events around every kernel launch of this Warper (bench.py's roofline leg)."""
+        _lib.check(self._lib.tcw_profile_enable(self._context(), int(enable)), "tcw_profile_enable")
+
+    def profile_read(self):
+        """-> {kernel: (total_ms, launches, units)} since the last read; synchronises."""
+        ms = (ctypes.c_double * 3)()
+        n = (ctypes.c_longlong * 3)()
+        units = (ctypes.c_double * 3)()
+        _lib.check(self._lib.tcw_profile_read(self._context(), ms, n, units), "tcw_profile_read")
+        names = ("zmax", "project_splat", "normalise")
+        return {k: (ms[i], int(n[i]), units[i]) for i, k in enumerate(names)}
+
     # ------------------------------------------------------------------ batched fast entry
     def forward_warp_batch(self, frames: torch.Tensor, depths: torch.Tensor,
                            transformation1: torch.Tensor, transformation2: torch.Tensor,
@@ -107,10 +120,14 @@ class Warper:
     def forward_warp_matrices(self, frames: torch.Tensor, depths: torch.Tensor, M: torch.Tensor,
                               mask1: Optional[torch.Tensor] = None, src_index: Optional[torch.Tensor] = None,
                               per_frame_max: bool = True, mask: bool = False,
-                              return_depth: bool = True, return_flow: bool = True, check_range: bool = True,
-                              deterministic: bool = False):
+                              return_depth: bool = True, return_flow: bool = True, check_range=True,
+                              deterministic: bool = False, out=None):
         """``forward_warp_batch`` on an already prepared (n_units,30) matrix block
-        (``prepare_matrices``): [K1^-1 | rows 0..2 of T2*T1^-1 | K2] per unit."""
+        (``prepare_matrices``): [K1^-1 | rows 0..2 of T2*T1^-1 | K2] per unit.
+
+        ``check_range`` True: raise AssertionError like the reference if a colour left [-1.1,1.1]
+        (one host sync); False: skip; an int32 CUDA tensor: OR the flag into it, no sync (check it
+        later).  ``out`` may carry preallocated (frame, mask, depth|None, flow|None) CUDA tensors."""
         n_src, c, h, w = frames.shape
         n = M.shape[0]
         assert c == 3 and depths.shape == (n_src, 1, h, w) and M.shape == (n, 30)
@@ -127,11 +144,23 @@ class Warper:
         flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) \
             | (_lib.TCW_DETERMINISTIC if deterministic else 0)
         odt = torch.float64 if mask else torch.float32
-        out_frame = torch.empty((n, 3, h, w), dtype=odt, device=self.device)
-        out_mask = torch.empty((n, 1, h, w), dtype=odt, device=self.device)
-        out_depth = torch.empty((n, 1, h, w), dtype=torch.float32, device=self.device) if return_depth else None
-        out_flow = torch.empty((n, 2, h, w), dtype=torch.float32, device=self.device) if return_flow else None
-        flag = torch.zeros(1, dtype=torch.int32, device=self.device) if check_range else None
+        if out is not None:
+            out_frame, out_mask, out_depth, out_flow = out
+            assert out_frame.shape == (n, 3, h, w) and out_frame.dtype == odt and out_frame.is_contiguous()
+            assert out_mask.shape == (n, 1, h, w) and out_mask.dtype == odt and out_mask.is_contiguous()
+            assert out_depth is None or (out_depth.shape == (n, 1, h, w) and out_depth.is_contiguous())
+            assert out_flow is None or (out_flow.shape == (n, 2, h, w) and out_flow.is_contiguous())
+        else:
+            out_frame = torch.empty((n, 3, h, w), dtype=odt, device=self.device)
+            out_mask = torch.empty((n, 1, h, w), dtype=odt, device=self.device)
+            out_depth = torch.empty((n, 1, h, w), dtype=torch.float32, device=self.device) if return_depth else None
+            out_flow = torch.empty((n, 2, h, w), dtype=torch.float32, device=self.device) if return_flow else None
+        lazy_flag = isinstance(check_range, torch.Tensor)
+        if lazy_flag:
+            flag = check_range
+            assert flag.dtype == torch.int32 and flag.is_cuda
+        else:
+            flag = torch.zeros(1, dtype=torch.int32, device=self.device) if check_range else None
         ws = self._get_workspace(n, h, w, flags)
         with torch.cuda.device(self.device):
             rc = self._lib.tcw_forward_warp(self._context(), _ptr(frames_d), _ptr(mask1_d), _ptr(depths_d),
@@ -139,7 +168,7 @@ class Warper:
                                             _ptr(out_frame), _ptr(out_mask), _ptr(out_depth), _ptr(out_flow),
                                             _ptr(flag), _ptr(ws), ws.numel(), self._stream())
         _lib.check(rc, "tcw_forward_warp")
-        if check_range:
+        if flag is not None and not lazy_flag:
             # the reference asserts -1.1 <= warped <= 1.1 before clipping (models/utils.py:580-581)
             assert int(flag.item()) == 0
         return out_frame, out_mask, out_depth, out_flow
