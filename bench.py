@@ -194,7 +194,7 @@ def run_ours(args):
 
     def step():
         warper.forward_warp_matrices(frames_d, depths_d, M, src_index=src, per_frame_max=True,
-                                     check_range=flag, out=out)
+                                     check_range=flag, out=out, deterministic=args.deterministic)
 
     for _ in range(max(3, args.warmup)):
         step()
@@ -227,7 +227,7 @@ def run_ours(args):
     if k_n:
         achieved = ALGO_BYTES_PER_PX * k_units * H * W / (k_ms * 1e-3) / 1e9
         total_k_ms = sum(v[0] for v in prof.values())
-        roofline = {"bound": "hbm", "kernel": "k_project_splat_f32", "achieved": achieved, "peak": peak,
+        roofline = {"bound": "hbm", "kernel": "k_project_splat<i64>" if args.deterministic else "k_project_splat<f32>", "achieved": achieved, "peak": peak,
                     "unit": "GB/s", "frac": achieved / peak, "traffic": None,
                     "peak_source": peak_src, "avg_launch_us": k_ms / k_n * 1e3, "launches": k_n,
                     "algorithmic_bytes_per_launch": ALGO_BYTES_PER_PX * k_units * H * W / k_n,
@@ -293,7 +293,8 @@ def run_ours(args):
             "metric": "warped_mpix_per_s", "value": value, "unit": "Mpix/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": workload_config(), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "config": dict(workload_config(), accumulation="int64 fixed point (deterministic)" if args.deterministic
+                           else "fp32 L2 reductions"), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "cpu_baseline": cpu_baseline,
         }
         if gather is not None:
@@ -310,6 +311,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--deterministic", action="store_true", help="order-independent int64 accumulation")
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -53,8 +53,8 @@ long long tcw_launch_count(const tcw_ctx* ctx);
 /*
  * Optional per-kernel device timing (CUDA events around every launch, on the launching stream).
  * tcw_profile_read synchronises on the recorded events, sums them per kernel class
- * [0]=depth-max pre-pass, [1]=project+splat, [2]=normalise, and resets the log.
- * ms/launches/units are arrays of 3; units = number of warp units those launches processed.
+ * [0]=depth-max pre-pass, [1]=project+splat, [2]=normalise, [3]=max-weight pre-pass of the
+ * deterministic path, and resets the log.  ms/launches/units are arrays of 4; units = number of warp units those launches processed.
  */
 int tcw_profile_enable(tcw_ctx* ctx, int enable);
 int tcw_profile_read(tcw_ctx* ctx, double* ms, long long* launches, double* units);

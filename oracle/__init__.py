@@ -116,3 +116,13 @@ def clean_points(frame, mask2):
                                 om.ctypes.data_as(ctypes.POINTER(ctypes.c_double)))
     assert rc == 0, rc
     return of, om
+
+
+def contrib_count(flow):
+    """Contributions per output pixel (b,1,h,w) int32 for a flow field (b,2,h,w); see orc_contrib_count."""
+    flow = _f32(flow)
+    b, _, h, w = flow.shape
+    out = np.zeros((b, 1, h, w), np.int32)
+    rc = lib().orc_contrib_count(_fp(flow), b, h, w, out.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
+    assert rc == 0, rc
+    return out

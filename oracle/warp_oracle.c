@@ -276,3 +276,30 @@ ORC_EXPORT int orc_clean_points(const float* frame, const float* mask2, int c, i
     free(hole);
     return 0;
 }
+
+/*
+ * Number of scatter contributions each output pixel receives (4 corners per source pixel, the same
+ * indices as orc_splat; models/utils.py:450-475, 524-564).  Test infrastructure for the parity
+ * tolerance: the reference accumulates sequentially in fp32, so a cell with n contributors carries
+ * a rounding error of up to ~n*2^-24 relative in the reference itself; tests widen the 1e-5
+ * tolerance by that bound for cells with n > 64 (fold lines, the behind-camera pixel (1,1)).
+ */
+ORC_EXPORT int orc_contrib_count(const float* flow, int b, int h, int w, int* out) {
+    const size_t hw = (size_t)h * w;
+    memset(out, 0, sizeof(int) * hw * b);
+    for (int n = 0; n < b; ++n) {
+        const float* fl = flow + (size_t)n * 2 * hw;
+        for (int y = 0; y < h; ++y) for (int x = 0; x < w; ++x) {
+            size_t p = (size_t)y * w + x;
+            float ox = (fl[p] + (float)x) + 1.0f;
+            float oy = (fl[hw + p] + (float)y) + 1.0f;
+            int ix[2] = {clamp_index(floorf(ox), w + 1), clamp_index(ceilf(ox), w + 1)};
+            int iy[2] = {clamp_index(floorf(oy), h + 1), clamp_index(ceilf(oy), h + 1)};
+            for (int k = 0; k < 4; ++k) {
+                int cx = ix[k >> 1], cy = iy[k & 1];
+                if (cx >= 1 && cx <= w && cy >= 1 && cy <= h) out[(size_t)n * hw + (size_t)(cy - 1) * w + (cx - 1)]++;
+            }
+        }
+    }
+    return 0;
+}

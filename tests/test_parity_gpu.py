@@ -28,20 +28,23 @@ def npy(t):
 def check_against(got, ref_frame, ref_mask, ref_depth, ref_flow, tol=1e-5):
     gf, gm, gd, gfl = [npy(t) for t in got]
     assert bit_equal(gm.astype(ref_mask.dtype), ref_mask), "validity mask must be bit-exact"
+    count = None
     if ref_flow is not None:
         assert bit_equal(gfl, ref_flow), "flow12 must be bit-exact"
-    e1 = assert_colour_close(gf, ref_frame, tol=tol)
-    e2 = assert_depth_close(gd, ref_depth, ref_mask, rtol=tol)
+        count = oracle.contrib_count(ref_flow)      # widens the tolerance only where > 64 contributions meet
+    e1 = assert_colour_close(gf, ref_frame, tol=tol, count=count)
+    e2 = assert_depth_close(gd, ref_depth, ref_mask, rtol=tol, count=count)
     return e1, e2
 
 
+@pytest.mark.parametrize("det", [False, True], ids=["f32", "det"])
 @pytest.mark.parametrize("name", warp_case_names(twice=False, clean=False))
-def test_golden_forward_warp(warper, golden, name):
+def test_golden_forward_warp(warper, golden, name, det):
     """CUDA vs outputs of the unmodified reference (fixtures), on the stored matrix block."""
     c = golden[name]
     b = c["frame"].shape[0]
     got = warper.forward_warp_matrices(T(c["frame"]), T(c["depth"]), T(c["M"]), mask1=T(c.get("mask1")),
-                                       per_frame_max=(b == 1))
+                                       per_frame_max=(b == 1), deterministic=det)
     check_against(got, c["out_frame"], c["out_mask"], c["out_depth"], c["out_flow"])
 
 
@@ -72,11 +75,12 @@ def test_golden_projection_bit_exact(warper, golden, name):
     assert pts.shape == (b, h, w, 3, 1)
 
 
+@pytest.mark.parametrize("det", [False, True], ids=["f32", "det"])
 @pytest.mark.parametrize("name", warp_case_names(twice=False, clean=True))
-def test_golden_mask_true(warper, golden, name):
+def test_golden_mask_true(warper, golden, name, det):
     """mask=True: fused clean_points, float64 outputs, cleaned pixels exactly -1 (H7)."""
     c = golden[name]
-    got = warper.forward_warp_matrices(T(c["frame"]), T(c["depth"]), T(c["M"]), mask=True)
+    got = warper.forward_warp_matrices(T(c["frame"]), T(c["depth"]), T(c["M"]), mask=True, deterministic=det)
     assert got[0].dtype == torch.float64 and got[1].dtype == torch.float64
     gf, gm, gd, gfl = [npy(t) for t in got]
     assert bit_equal(gm, c["out_mask"])
@@ -131,13 +135,14 @@ def clip():
     return synthetic_clip(49, 384, 672, seed=1234)
 
 
-def test_full_size_vs_oracle_orbits(warper, clip):
+@pytest.mark.parametrize("det", [False, True], ids=["f32", "det"])
+def test_full_size_vs_oracle_orbits(warper, clip, det):
     """BASELINE config 2 at full resolution on a subset of units: frames {0,24,48} x 8 orbit presets."""
     frames, depths = clip
     T1, T2, K, src = orbit_units(depths, 384, 672)
     pick = torch.cat([torch.arange(8) + 8 * f for f in (0, 24, 48)])
     M = prepare_matrices(T1[pick], T2[pick], K[pick])
-    got = warper.forward_warp_matrices(frames, depths, M, src_index=src[pick])
+    got = warper.forward_warp_matrices(frames, depths, M, src_index=src[pick], deterministic=det)
     ref = oracle.forward_warp(frames, None, depths, M, src_index=src[pick].numpy(), per_unit_max=True)
     e = check_against(got, ref[0], ref[1], ref[2], ref[3])
     print("config2 subset: colour max|d| %.2e depth max rel %.2e" % e)
@@ -154,7 +159,28 @@ def test_full_size_per_unit_equals_single_calls(warper, clip):
         assert_colour_close(npy(one[0]), npy(batch[0][i:i + 1]))
 
 
-def test_1080p_stress_vs_oracle(warper):
+def test_deterministic_mode_is_bitwise_reproducible(warper, clip):
+    """TCW_DETERMINISTIC: integer accumulation is order-independent, so two runs (and two different
+    chunkings of the same units) give bit-identical outputs; the fp32 path agrees within tolerance."""
+    frames, depths = clip
+    T1, T2, K, src = orbit_units(depths, 384, 672)
+    pick = torch.cat([torch.arange(8) + 8 * f for f in (10, 30, 47, 48)])
+    M = prepare_matrices(T1[pick], T2[pick], K[pick])
+    a = warper.forward_warp_matrices(frames, depths, M, src_index=src[pick], deterministic=True)
+    b = warper.forward_warp_matrices(frames, depths, M, src_index=src[pick], deterministic=True)
+    for x, y in zip(a, b):
+        assert torch.equal(x, y)
+    half = warper.forward_warp_matrices(frames, depths, M[:5], src_index=src[pick][:5], deterministic=True)
+    for x, y in zip(a, half):
+        assert torch.equal(x[:5], y)
+    f = warper.forward_warp_matrices(frames, depths, M, src_index=src[pick], deterministic=False)
+    assert torch.equal(a[1], f[1]) and torch.equal(a[3], f[3])
+    assert_colour_close(npy(f[0]), npy(a[0]))
+    assert_depth_close(npy(f[2]), npy(a[2]), npy(a[1]))
+
+
+@pytest.mark.parametrize("det", [False, True], ids=["f32", "det"])
+def test_1080p_stress_vs_oracle(warper, det):
     """BASELINE config 3: 1080p, (0,30,0.3) trajectory + contention stress (25% behind the camera)."""
     frames, depths = synthetic_clip(2, 1080, 1920, seed=5)
     T1, T2, K, src = orbit_units(depths, 1080, 1920, d_r=0.3, presets=[(0, 30)])
@@ -163,7 +189,7 @@ def test_1080p_stress_vs_oracle(warper):
     depths[1, :, :, :480] = 0.0           # zero depth: with the 30 degree orbit these stay in front ...
     M = prepare_matrices(T1, T2, K)
     M[1, 9:21] = prepare_matrices(T1[:1], torch.diag(torch.tensor([-1.0, 1, -1, 1]))[None] @ T2[:1], K[:1])[0, 9:21]
-    got = warper.forward_warp_matrices(frames, depths, M)   # ... unit 1 looks backwards: everything is behind
+    got = warper.forward_warp_matrices(frames, depths, M, deterministic=det)   # ... unit 1 looks backwards: everything is behind
     ref = oracle.forward_warp(frames, None, depths, M, per_unit_max=True)
     check_against(got, ref[0], ref[1], ref[2], ref[3])
 

@@ -49,7 +49,7 @@ struct tcw_ctx {
     int prof_n, prof_cap;
 };
 
-enum { PK_ZMAX = 0, PK_SPLAT = 1, PK_NORMALISE = 2, PK_COUNT = 3 };
+enum { PK_ZMAX = 0, PK_SPLAT = 1, PK_NORMALISE = 2, PK_WMAX = 3, PK_COUNT = 4 };
 
 static void prof_begin(tcw_ctx* ctx, int kernel, double units, cudaStream_t st) {
     if (!ctx->prof_on) return;
@@ -217,143 +217,7 @@ __device__ __forceinline__ float block_max_256(float v) {
     return v;   // valid in thread 0
 }
 
-// ----------------------------------------------------------------------------------------------
-// K0: per-unit max of log(1+sat(z'))  — the soft-z normaliser  (models/utils.py:492)
-//   grid (tiles, n_units); reads depth only (4 B/px).
-// ----------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TILE_THREADS)
-k_zmax(const float* __restrict__ depth, const int* __restrict__ src_index, const float* __restrict__ Mall,
-       int unit0, int h, int w, int tiles_x, unsigned* __restrict__ Lbits, int n_units_total) {
-    __shared__ float M[M_FLOATS];
-    const int u = unit0 + blockIdx.y;
-    if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
-    __syncthreads();
-    const int s = src_index ? src_index[u] : u;
-    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
-    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
-    float ld = 0.0f;
-    if (x < w && y < h) {
-        float d = depth[(size_t)s * h * w + (size_t)y * w + x];
-        float P0, P1, P2;
-        project_px(M, (float)x, (float)y, d, P0, P1, P2);
-        ld = log_depth(P2);
-    }
-    float m = block_max_256(ld);
-    if (threadIdx.x == 0) {
-        // ld >= 0, so the float order equals the unsigned order of the bit patterns
-        atomicMax(&Lbits[u], __float_as_uint(m));
-        atomicMax(&Lbits[n_units_total], __float_as_uint(m));
-    }
-}
-
-// ----------------------------------------------------------------------------------------------
-// K2 (v1): fused unproject/transform/project + bilinear soft-z splat, fp32 L2 reductions.
-//   acc: [unit in chunk][NCH][h*w] fp32, pad ring dropped (it is cropped at :568-569).
-// ----------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(TILE_THREADS)
-k_project_splat_f32(const float* __restrict__ frame, const float* __restrict__ mask1,
-                    const float* __restrict__ depth, const int* __restrict__ src_index,
-                    const float* __restrict__ Mall, int unit0, int h, int w, int tiles_x,
-                    const unsigned* __restrict__ Lbits, int l_index_global /* -1: per unit */,
-                    float* __restrict__ acc, float* __restrict__ out_flow) {
-    __shared__ float M[M_FLOATS];
-    const int uc = blockIdx.y, u = unit0 + uc;
-    if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
-    __syncthreads();
-    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
-    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
-    if (x >= w || y >= h) return;
-    const int s = src_index ? src_index[u] : u;
-    const size_t hw = (size_t)h * w, p = (size_t)y * w + x;
-    const float d = depth[(size_t)s * hw + p];
-    float P0, P1, P2;
-    project_px(M, (float)x, (float)y, d, P0, P1, P2);
-    // coords = P.xy / P.z ; flow12 = coords - grid   (models/utils.py:273-278)
-    const float flx = __fsub_rn(__fdiv_rn(P0, P2), (float)x);
-    const float fly = __fsub_rn(__fdiv_rn(P1, P2), (float)y);
-    if (out_flow) {
-        out_flow[(size_t)u * 2 * hw + p] = flx;
-        out_flow[(size_t)u * 2 * hw + hw + p] = fly;
-    }
-    const Corners c = corners_from_flow(flx, fly, x, y, h, w);
-    const float L = __uint_as_float(Lbits[l_index_global >= 0 ? l_index_global : u]);
-    const float g = expf(__fmul_rn(__fdiv_rn(log_depth(P2), L), 50.0f));   // :492
-    const float m = mask1 ? mask1[(size_t)s * hw + p] : 1.0f;
-    const float r = frame[((size_t)s * 3 + 0) * hw + p];
-    const float gch = frame[((size_t)s * 3 + 1) * hw + p];
-    const float b = frame[((size_t)s * 3 + 2) * hw + p];
-    float* a = acc + (size_t)uc * NCH * hw;
-    #pragma unroll
-    for (int k = 0; k < 4; ++k) {
-        const int cx = (k & 2) ? c.ix1 : c.ix0;
-        const int cy = (k & 1) ? c.iy1 : c.iy0;
-        if (cx < 1 || cx > w || cy < 1 || cy > h) continue;          // pad ring: cropped away
-        const float prox = k == 0 ? c.nw : (k == 1 ? c.sw : (k == 2 ? c.ne : c.se));
-        const float wk = __fdiv_rn(__fmul_rn(prox, m), g);            // :494-513
-        const size_t cell = (size_t)(cy - 1) * w + (cx - 1);
-        atomicAdd(a + 0 * hw + cell, __fmul_rn(r, wk));
-        atomicAdd(a + 1 * hw + cell, __fmul_rn(gch, wk));
-        atomicAdd(a + 2 * hw + cell, __fmul_rn(b, wk));
-        atomicAdd(a + 3 * hw + cell, __fmul_rn(P2, wk));
-        atomicAdd(a + 4 * hw + cell, wk);
-    }
-}
-
-// ----------------------------------------------------------------------------------------------
-// K3: normalise / mask / clip (+ optional fused clean_points)   (models/utils.py:566-583, 585-626)
-// ----------------------------------------------------------------------------------------------
-template <bool CLEAN>
-__global__ void __launch_bounds__(TILE_THREADS)
-k_normalise(const float* __restrict__ acc, int unit0, int h, int w, int tiles_x,
-            void* __restrict__ out_frame, void* __restrict__ out_mask, float* __restrict__ out_depth,
-            int* __restrict__ range_flag) {
-    const int uc = blockIdx.y, u = unit0 + uc;
-    const int x = (blockIdx.x % tiles_x) * TILE_W + (threadIdx.x % TILE_W);
-    const int y = (blockIdx.x / tiles_x) * TILE_H + (threadIdx.x / TILE_W);
-    if (x >= w || y >= h) return;
-    const size_t hw = (size_t)h * w, p = (size_t)y * w + x;
-    const float* a = acc + (size_t)uc * NCH * hw;
-    const float W = a[4 * hw + p];
-    const bool valid = W > 0.0f;
-    float col[3];
-    bool bad = false;
-    #pragma unroll
-    for (int ch = 0; ch < 3; ++ch) {
-        float v = valid ? __fdiv_rn(a[ch * hw + p], W) : -1.0f;
-        bad |= !(v >= -1.1f) || !(v <= 1.1f);
-        col[ch] = clampf(v, -1.0f, 1.0f);
-    }
-    if (bad && range_flag) atomicOr(range_flag, 1);
-    if (out_depth) out_depth[(size_t)u * hw + p] = valid ? __fdiv_rn(a[3 * hw + p], W) : 0.0f;
-    if (!CLEAN) {
-        float* of = (float*)out_frame;
-        #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) of[((size_t)u * 3 + ch) * hw + p] = col[ch];
-        ((float*)out_mask)[(size_t)u * hw + p] = valid ? 1.0f : 0.0f;
-    } else {
-        // clean_points: hole mask dilated 5x5 (outside pixels never win), float64 outputs
-        bool hole = false;
-        #pragma unroll
-        for (int dy = -2; dy <= 2; ++dy) {
-            const int yy = y + dy;
-            if (yy < 0 || yy >= h) continue;
-            #pragma unroll
-            for (int dx = -2; dx <= 2; ++dx) {
-                const int xx = x + dx;
-                if (xx < 0 || xx >= w) continue;
-                hole |= !(a[4 * hw + (size_t)yy * w + xx] > 0.0f);
-            }
-        }
-        const double keep = hole ? 0.0 : 1.0;
-        double* of = (double*)out_frame;
-        #pragma unroll
-        for (int ch = 0; ch < 3; ++ch) {
-            const float half = __fdiv_rn(__fadd_rn(col[ch], 1.0f), 2.0f);
-            of[((size_t)u * 3 + ch) * hw + p] = __dsub_rn(__dmul_rn(__dmul_rn((double)half, keep), 2.0), 1.0);
-        }
-        ((double*)out_mask)[(size_t)u * hw + p] = keep;
-    }
-}
+#include "warp_kernels.cuh"
 
 // ----------------------------------------------------------------------------------------------
 // compute_transformed_points as a standalone op
@@ -479,12 +343,15 @@ k_clean_points(const float* __restrict__ frame, const float* __restrict__ mask2,
 // host side of the C ABI
 // ----------------------------------------------------------------------------------------------
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-static size_t header_bytes(int n_units) { return align_up((size_t)(n_units + 1) * sizeof(unsigned), 256); }
+static size_t header_bytes(int n_units) { return align_up((size_t)(n_units + 1) * sizeof(UnitStats), 256); }
 
-// units per chunk: keep one chunk's accumulators + inputs + outputs (~64 B/px) inside L2
-static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, int planes) {
+// accumulator bytes per pixel of one unit: fp32 path 5 planes x 4 B; deterministic path 5 x int64 + max-weight plane
+static size_t acc_bytes_per_px(int flags) { return (flags & TCW_DETERMINISTIC) ? (size_t)NCH * 8 + 4 : (size_t)NCH * 4; }
+
+// units per chunk: keep one chunk's accumulators + inputs + outputs inside a fraction of L2
+static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, size_t acc_per_px) {
     if (ctx->chunk_units_override > 0) return ctx->chunk_units_override < n_units ? ctx->chunk_units_override : n_units;
-    const size_t per_unit = (size_t)h * w * (size_t)(4 * planes + 44);
+    const size_t per_unit = (size_t)h * w * (acc_per_px + 44);
     size_t budget = ctx->l2_bytes ? ctx->l2_bytes * 6 / 10 : (size_t)64 << 20;
     int g = (int)(budget / per_unit);
     if (g < 1) g = 1;
@@ -492,10 +359,10 @@ static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, int p
 }
 
 TCW_API int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, int flags, size_t* bytes) {
-    (void)flags;
     if (!ctx || !bytes || n_units <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_workspace_bytes: bad argument");
-    const int g = auto_chunk_units(ctx, n_units, h, w, NCH);
-    *bytes = header_bytes(n_units) + (size_t)g * NCH * h * w * sizeof(float);
+    const size_t per_px = acc_bytes_per_px(flags);
+    const int g = auto_chunk_units(ctx, n_units, h, w, per_px);
+    *bytes = header_bytes(n_units) + align_up((size_t)g * per_px * h * w, 256);
     return TCW_OK;
 }
 
@@ -515,47 +382,77 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     if (!frame || !depth || !M || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_forward_warp: NULL buffer");
     if (n_units <= 0 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp: bad shape");
     if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp: src_index is NULL but n_src != n_units");
-    if (flags & TCW_DETERMINISTIC) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_DETERMINISTIC not available in this build");
+    const bool det = flags & TCW_DETERMINISTIC;
     const size_t hw = (size_t)h * w;
     const size_t hdr = header_bytes(n_units);
-    if (!workspace || workspace_bytes < hdr + NCH * hw * sizeof(float))
+    const size_t unit_bytes = acc_bytes_per_px(flags) * hw;
+    if (!workspace || workspace_bytes < hdr + unit_bytes)
         return fail(TCW_E_WORKSPACE, "tcw_forward_warp: workspace too small (see tcw_workspace_bytes)");
     cudaStream_t st = (cudaStream_t)cuda_stream;
-    int g = (int)((workspace_bytes - hdr) / (NCH * hw * sizeof(float)));
-    const int want = auto_chunk_units(ctx, n_units, h, w, NCH);
+    int g = (int)((workspace_bytes - hdr) / unit_bytes);
+    const int want = auto_chunk_units(ctx, n_units, h, w, acc_bytes_per_px(flags));
     if (g > want) g = want;
-    unsigned* Lbits = (unsigned*)workspace;
-    float* acc = (float*)((char*)workspace + hdr);
+    UnitStats* stats = (UnitStats*)workspace;
+    char* accbase = (char*)workspace + hdr;
+    // chunk layout: fp32: [g][5][hw] float;  deterministic: [g][5][hw] int64 then [g][hw] uint32 max-weight bits
+    float* acc_f32 = det ? nullptr : (float*)accbase;
+    long long* acc_i64 = det ? (long long*)accbase : nullptr;
+    unsigned* wmax = det ? (unsigned*)(accbase + (size_t)g * NCH * hw * sizeof(long long)) : nullptr;
+    const float det_scale = det ? ldexpf(1.0f, det_shift(h, w)) : 0.0f;
     const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
     const bool per_unit = flags & TCW_PER_UNIT_MAX;
-    CUDA_TRY(cudaMemsetAsync(Lbits, 0, hdr, st));
+    const int sidx = per_unit ? -1 : n_units;
+    CUDA_TRY(cudaMemsetAsync(stats, 0, hdr, st));
     if (!per_unit) {   // the call-wide max needs every unit's depth pass first
         for (int u0 = 0; u0 < n_units; u0 += 65535) {
             const int nu = n_units - u0 < 65535 ? n_units - u0 : 65535;
-            k_zmax<<<dim3(tiles_x * tiles_y, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, Lbits, n_units);
+            prof_begin(ctx, PK_ZMAX, nu, st);
+            k_zmax<<<dim3(tiles_x * tiles_y, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, stats, n_units);
+            prof_end(ctx, st);
             LAUNCH_CHECK("k_zmax");
         }
     }
     for (int u0 = 0; u0 < n_units; u0 += g) {
         const int nu = n_units - u0 < g ? n_units - u0 : g;
         const dim3 grid(tiles_x * tiles_y, nu);
-        CUDA_TRY(cudaMemsetAsync(acc, 0, (size_t)nu * NCH * hw * sizeof(float), st));
+        if (det) {
+            CUDA_TRY(cudaMemsetAsync(acc_i64, 0, (size_t)nu * NCH * hw * sizeof(long long), st));
+            CUDA_TRY(cudaMemsetAsync(wmax, 0, (size_t)nu * hw * sizeof(unsigned), st));
+        } else {
+            CUDA_TRY(cudaMemsetAsync(acc_f32, 0, (size_t)nu * NCH * hw * sizeof(float), st));
+        }
         if (per_unit) {
             prof_begin(ctx, PK_ZMAX, nu, st);
-            k_zmax<<<grid, TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, Lbits, n_units);
+            k_zmax<<<grid, TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, stats, n_units);
             prof_end(ctx, st);
             LAUNCH_CHECK("k_zmax");
         }
-        prof_begin(ctx, PK_SPLAT, nu, st);
-        k_project_splat_f32<<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
-                                                          Lbits, per_unit ? -1 : n_units, acc, out_flow);
-        prof_end(ctx, st);
-        LAUNCH_CHECK("k_project_splat_f32");
+        if (det) {
+            prof_begin(ctx, PK_WMAX, nu, st);
+            k_project_splat<MODE_WMAX><<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
+                                                                    stats, sidx, nullptr, nullptr, wmax, det_scale, nullptr);
+            prof_end(ctx, st);
+            LAUNCH_CHECK("k_project_splat<wmax>");
+            prof_begin(ctx, PK_SPLAT, nu, st);
+            k_project_splat<MODE_I64><<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
+                                                                   stats, sidx, nullptr, acc_i64, wmax, det_scale, out_flow);
+            prof_end(ctx, st);
+            LAUNCH_CHECK("k_project_splat<i64>");
+        } else {
+            prof_begin(ctx, PK_SPLAT, nu, st);
+            k_project_splat<MODE_F32><<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
+                                                                   stats, sidx, acc_f32, nullptr, nullptr, 0.0f, out_flow);
+            prof_end(ctx, st);
+            LAUNCH_CHECK("k_project_splat<f32>");
+        }
         prof_begin(ctx, PK_NORMALISE, nu, st);
-        if (flags & TCW_CLEAN)
-            k_normalise<true><<<grid, TILE_THREADS, 0, st>>>(acc, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
-        else
-            k_normalise<false><<<grid, TILE_THREADS, 0, st>>>(acc, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
+        const bool clean = flags & TCW_CLEAN;
+        #define NORM_ARGS acc_f32, acc_i64, stats, sidx, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag
+        if (clean && det) k_normalise<true, true><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
+        else if (clean)   k_normalise<true, false><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
+        else if (det)     k_normalise<false, true><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
+        else              k_normalise<false, false><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
+        #undef NORM_ARGS
         prof_end(ctx, st);
         LAUNCH_CHECK("k_normalise");
     }
@@ -578,11 +475,11 @@ static int splat_c(tcw_ctx* ctx, const float* frame, const float* mask1, const f
                    const float* flow_mask, int b, int h, int w, int flags, float* out, float* out_mask,
                    int* range_flag, void* workspace, size_t workspace_bytes, cudaStream_t st) {
     const size_t hw = (size_t)h * w;
-    const size_t hdr = header_bytes(b);
+    const size_t hdr = header_bytes(b);      // used here as an array of (b+1) uint32 log-depth maxima
     if (!workspace || workspace_bytes < hdr + (C + 1) * hw * sizeof(float))
         return fail(TCW_E_WORKSPACE, "tcw_splat: workspace too small (see tcw_workspace_bytes)");
     int g = (int)((workspace_bytes - hdr) / ((C + 1) * hw * sizeof(float)));
-    const int want = auto_chunk_units(ctx, b, h, w, C + 1);
+    const int want = auto_chunk_units(ctx, b, h, w, (size_t)(C + 1) * 4);
     if (g > want) g = want;
     unsigned* Lbits = (unsigned*)workspace;
     float* acc = (float*)((char*)workspace + hdr);
@@ -692,7 +589,7 @@ TCW_API int tcw_forward_warp_host(tcw_ctx* ctx, const float* frame, const float*
     float* d_ofl = out_flow ? (float*)(base + o_ofl) : nullptr;
 
     // slices of units: upload the sources a slice needs, run it, download its outputs
-    const int slice = auto_chunk_units(ctx, n_units, h, w, NCH) * 2;
+    const int slice = auto_chunk_units(ctx, n_units, h, w, acc_bytes_per_px(flags)) * 2;
     const int n_slices = (n_units + slice - 1) / slice;
     cudaEvent_t* ev_in = (cudaEvent_t*)calloc((size_t)n_slices * 2, sizeof(cudaEvent_t));
     if (!ev_in) return fail(TCW_E_NOMEM, "tcw_forward_warp_host: out of host memory");

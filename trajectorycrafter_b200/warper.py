@@ -83,11 +83,11 @@ class Warper:
 
     def profile_read(self):
         """-> {kernel: (total_ms, launches, units)} since the last read; synchronises."""
-        ms = (ctypes.c_double * 3)()
-        n = (ctypes.c_longlong * 3)()
-        units = (ctypes.c_double * 3)()
+        ms = (ctypes.c_double * 4)()
+        n = (ctypes.c_longlong * 4)()
+        units = (ctypes.c_double * 4)()
         _lib.check(self._lib.tcw_profile_read(self._context(), ms, n, units), "tcw_profile_read")
-        names = ("zmax", "project_splat", "normalise")
+        names = ("zmax", "project_splat", "normalise", "wmax")
         return {k: (ms[i], int(n[i]), units[i]) for i, k in enumerate(names)}
 
     # ------------------------------------------------------------------ batched fast entry
