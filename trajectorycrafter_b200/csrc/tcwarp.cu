@@ -39,6 +39,9 @@ struct tcw_ctx {
     size_t l2_bytes;
     long long launches;
     int chunk_units_override;   // TCW_CHUNK_UNITS env (0 = auto)
+    int pipeline_off;           // TCW_NO_PIPELINE env: use the per-chunk launches for the fp32 path too
+    int pipe_lag_override;      // TCW_PIPE_LAG env (0 = auto)
+    int pipe_blocks;            // resident CTAs of k_warp_pipeline on this device (0 = not queried yet)
     // resources of the host-buffer entry point (grow-only)
     cudaStream_t s_in, s_run, s_out;
     void* pool;
@@ -119,6 +122,10 @@ TCW_API int tcw_create(int device, tcw_ctx** out) {
     c->l2_bytes = (size_t)p.l2CacheSize;
     const char* env = getenv("TCW_CHUNK_UNITS");
     c->chunk_units_override = env ? atoi(env) : 0;
+    env = getenv("TCW_NO_PIPELINE");
+    c->pipeline_off = env ? atoi(env) : 0;
+    env = getenv("TCW_PIPE_LAG");
+    c->pipe_lag_override = env ? atoi(env) : 0;
     *out = c;
     return TCW_OK;
 }
@@ -218,6 +225,9 @@ __device__ __forceinline__ float block_max_256(float v) {
 }
 
 #include "warp_kernels.cuh"
+#include "warp_fast.cuh"
+#include "warp_strip.cuh"
+#include "warp_pipeline.cuh"
 
 // ----------------------------------------------------------------------------------------------
 // compute_transformed_points as a standalone op
@@ -343,7 +353,9 @@ k_clean_points(const float* __restrict__ frame, const float* __restrict__ mask2,
 // host side of the C ABI
 // ----------------------------------------------------------------------------------------------
 static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
-static size_t header_bytes(int n_units) { return align_up((size_t)(n_units + 1) * sizeof(UnitStats), 256); }
+// workspace header: 256 B of control words (ticket counter of the pipeline kernel) + per-unit stats (+1 for the whole call)
+constexpr size_t CTRL_BYTES = 256;
+static size_t header_bytes(int n_units) { return CTRL_BYTES + align_up((size_t)(n_units + 1) * sizeof(UnitStats), 256); }
 
 // accumulator bytes per pixel of one unit: fp32 path 5 planes x 4 B; deterministic path 5 x int64 + max-weight plane
 static size_t acc_bytes_per_px(int flags) { return (flags & TCW_DETERMINISTIC) ? (size_t)NCH * 8 + 4 : (size_t)NCH * 4; }
@@ -361,7 +373,8 @@ static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, size_
 TCW_API int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, int flags, size_t* bytes) {
     if (!ctx || !bytes || n_units <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_workspace_bytes: bad argument");
     const size_t per_px = acc_bytes_per_px(flags);
-    const int g = auto_chunk_units(ctx, n_units, h, w, per_px);
+    int g = auto_chunk_units(ctx, n_units, h, w, per_px);
+    if (!(flags & (TCW_DETERMINISTIC | TCW_CLEAN)) && g < PIPE_RING) g = PIPE_RING;   // accumulator ring of the pipeline kernel
     *bytes = header_bytes(n_units) + align_up((size_t)g * per_px * h * w, 256);
     return TCW_OK;
 }
@@ -390,69 +403,119 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         return fail(TCW_E_WORKSPACE, "tcw_forward_warp: workspace too small (see tcw_workspace_bytes)");
     cudaStream_t st = (cudaStream_t)cuda_stream;
     int g = (int)((workspace_bytes - hdr) / unit_bytes);
+    const bool ring_fits = g >= PIPE_RING;
     const int want = auto_chunk_units(ctx, n_units, h, w, acc_bytes_per_px(flags));
     if (g > want) g = want;
-    UnitStats* stats = (UnitStats*)workspace;
+    UnitStats* stats = (UnitStats*)((char*)workspace + CTRL_BYTES);
+    int* ticket = (int*)workspace;
     char* accbase = (char*)workspace + hdr;
-    // chunk layout: fp32: [g][5][hw] float;  deterministic: [g][5][hw] int64 then [g][hw] uint32 max-weight bits
-    float* acc_f32 = det ? nullptr : (float*)accbase;
+    // chunk layout: fp32: [g][hw] float4 (sum w*r,g,b,z) then [g][hw] float (sum w);
+    //               deterministic: [g][5][hw] int64 then [g][hw] uint32 max-weight bits
+    float4* acc4 = det ? nullptr : (float4*)accbase;
+    float* accw = det ? nullptr : (float*)(accbase + (size_t)g * hw * sizeof(float4));
     long long* acc_i64 = det ? (long long*)accbase : nullptr;
     unsigned* wmax = det ? (unsigned*)(accbase + (size_t)g * NCH * hw * sizeof(long long)) : nullptr;
     const float det_scale = det ? ldexpf(1.0f, det_shift(h, w)) : 0.0f;
     const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
+    const int strips_x = (w + STRIP_W - 1) / STRIP_W, strips_per_unit = strips_x * ((h + STRIP_H - 1) / STRIP_H);
+    const int strip_blocks = (strips_per_unit + TILE_THREADS / 32 - 1) / (TILE_THREADS / 32);
     const bool per_unit = flags & TCW_PER_UNIT_MAX;
+    const bool clean = flags & TCW_CLEAN;
     const int sidx = per_unit ? -1 : n_units;
-    CUDA_TRY(cudaMemsetAsync(stats, 0, hdr, st));
-    if (!per_unit) {   // the call-wide max needs every unit's depth pass first
+    CUDA_TRY(cudaMemsetAsync(workspace, 0, hdr, st));   // ticket + per-unit stats and counters
+    {   // K0: soft-z normaliser of every unit (and of the whole call) before any splat
+        const int quads = h * ((w + 3) / 4);
+        int bx = (quads + TILE_THREADS * 2 - 1) / (TILE_THREADS * 2);
+        if (bx < 1) bx = 1;
         for (int u0 = 0; u0 < n_units; u0 += 65535) {
             const int nu = n_units - u0 < 65535 ? n_units - u0 : 65535;
             prof_begin(ctx, PK_ZMAX, nu, st);
-            k_zmax<<<dim3(tiles_x * tiles_y, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, stats, n_units);
+            k_zmax_quad<<<dim3(bx, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, stats, n_units);
             prof_end(ctx, st);
-            LAUNCH_CHECK("k_zmax");
+            LAUNCH_CHECK("k_zmax_quad");
         }
     }
+    // the plain fp32 normalise kernel re-zeroes what it read: one memset per call instead of one per chunk
+    const bool rezero = !det && !clean;
+    const bool vec = (hw % 4 == 0) && ((((size_t)accbase) | ((size_t)out_frame) | ((size_t)out_mask) | ((size_t)out_depth)) % 16 == 0);
+    SplatArgs A;
+    A.frame = frame; A.mask1 = mask1; A.depth = depth; A.src_index = src_index; A.Mall = M;
+    A.h = h; A.w = w; A.strips_x = strips_x; A.strips_per_unit = strips_per_unit;
+    A.stats = stats; A.stat_index_global = sidx;
+    A.acc4 = acc4; A.accw = accw; A.acc_i64 = acc_i64; A.wmax = wmax; A.det_scale = det_scale; A.out_flow = out_flow;
+    if (rezero && !ctx->pipeline_off && ring_fits) {
+        // fp32 path: one persistent kernel runs splat + normalise of every unit (warp_pipeline.cuh)
+        if (!ctx->pipe_blocks) {
+            int per_sm = 0;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_warp_pipeline, TILE_THREADS, 0));
+            ctx->pipe_blocks = (per_sm > 0 ? per_sm : 1) * ctx->sm_count;
+        }
+        // ring layout: [PIPE_RING][hw] float4 then [PIPE_RING][hw] float
+        A.accw = (float*)(accbase + (size_t)PIPE_RING * hw * sizeof(float4));
+        CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)PIPE_RING * NCH * hw * sizeof(float), st));
+        PipeArgs P;
+        P.A = A; P.stats_rw = stats; P.ticket = ticket;
+        P.n_units = n_units; P.ns = strip_blocks; P.vec = vec ? 1 : 0;
+        P.nn = (int)(((vec ? hw / 4 : hw) + NORM_ITEM - 1) / NORM_ITEM);
+        {   // lag: a full wave of resident CTAs between a unit's splat items and its normalise items
+            const int per_unit_items = P.ns + P.nn;
+            int lag = (ctx->pipe_blocks + per_unit_items - 1) / per_unit_items;
+            if (ctx->pipe_lag_override > 0) lag = ctx->pipe_lag_override;
+            if (lag < 1) lag = 1;
+            if (lag > PIPE_RING - 2) lag = PIPE_RING - 2;
+            P.lag = lag; P.ring = lag + 2;
+        }
+        P.out_frame = (float*)out_frame; P.out_mask = (float*)out_mask; P.out_depth = out_depth; P.range_flag = range_flag;
+        const long long items = (long long)n_units * (P.ns + P.nn);
+        if (items > 0x7fffff00ll) return fail(TCW_E_ARG, "tcw_forward_warp: too many work items for one call");
+        const int blocks = (long long)ctx->pipe_blocks < items ? ctx->pipe_blocks : (int)items;
+        prof_begin(ctx, PK_SPLAT, n_units, st);
+        k_warp_pipeline<<<blocks, TILE_THREADS, 0, st>>>(P);
+        prof_end(ctx, st);
+        LAUNCH_CHECK("k_warp_pipeline");
+        return TCW_OK;
+    }
+    if (rezero) CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)(g < n_units ? g : n_units) * NCH * hw * sizeof(float), st));
     for (int u0 = 0; u0 < n_units; u0 += g) {
         const int nu = n_units - u0 < g ? n_units - u0 : g;
-        const dim3 grid(tiles_x * tiles_y, nu);
+        const dim3 sgrid(strip_blocks, nu);
         if (det) {
             CUDA_TRY(cudaMemsetAsync(acc_i64, 0, (size_t)nu * NCH * hw * sizeof(long long), st));
             CUDA_TRY(cudaMemsetAsync(wmax, 0, (size_t)nu * hw * sizeof(unsigned), st));
-        } else {
-            CUDA_TRY(cudaMemsetAsync(acc_f32, 0, (size_t)nu * NCH * hw * sizeof(float), st));
-        }
-        if (per_unit) {
-            prof_begin(ctx, PK_ZMAX, nu, st);
-            k_zmax<<<grid, TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, tiles_x, stats, n_units);
-            prof_end(ctx, st);
-            LAUNCH_CHECK("k_zmax");
-        }
-        if (det) {
+            A.out_flow = nullptr;
             prof_begin(ctx, PK_WMAX, nu, st);
-            k_project_splat<MODE_WMAX><<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
-                                                                    stats, sidx, nullptr, nullptr, wmax, det_scale, nullptr);
+            k_splat_strip<MODE_WMAX><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
             prof_end(ctx, st);
-            LAUNCH_CHECK("k_project_splat<wmax>");
+            LAUNCH_CHECK("k_splat_strip<wmax>");
+            A.out_flow = out_flow;
             prof_begin(ctx, PK_SPLAT, nu, st);
-            k_project_splat<MODE_I64><<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
-                                                                   stats, sidx, nullptr, acc_i64, wmax, det_scale, out_flow);
+            k_splat_strip<MODE_I64><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
             prof_end(ctx, st);
-            LAUNCH_CHECK("k_project_splat<i64>");
+            LAUNCH_CHECK("k_splat_strip<i64>");
         } else {
+            if (!rezero) CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)g * NCH * hw * sizeof(float), st));
             prof_begin(ctx, PK_SPLAT, nu, st);
-            k_project_splat<MODE_F32><<<grid, TILE_THREADS, 0, st>>>(frame, mask1, depth, src_index, M, u0, h, w, tiles_x,
-                                                                   stats, sidx, acc_f32, nullptr, nullptr, 0.0f, out_flow);
+            k_splat_strip<MODE_F32><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
             prof_end(ctx, st);
-            LAUNCH_CHECK("k_project_splat<f32>");
+            LAUNCH_CHECK("k_splat_strip<f32>");
         }
         prof_begin(ctx, PK_NORMALISE, nu, st);
-        const bool clean = flags & TCW_CLEAN;
-        #define NORM_ARGS acc_f32, acc_i64, stats, sidx, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag
-        if (clean && det) k_normalise<true, true><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
-        else if (clean)   k_normalise<true, false><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
-        else if (det)     k_normalise<false, true><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
-        else              k_normalise<false, false><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
-        #undef NORM_ARGS
+        if (rezero) {
+            if (vec) {
+                k_normalise_quad<true><<<dim3((unsigned)((hw / 4 + TILE_THREADS - 1) / TILE_THREADS), nu), TILE_THREADS, 0, st>>>(
+                    acc4, accw, u0, hw, (float*)out_frame, (float*)out_mask, out_depth, range_flag);
+            } else {
+                k_normalise_quad<false><<<dim3((unsigned)((hw + TILE_THREADS - 1) / TILE_THREADS), nu), TILE_THREADS, 0, st>>>(
+                    acc4, accw, u0, hw, (float*)out_frame, (float*)out_mask, out_depth, range_flag);
+            }
+        } else {
+            const dim3 grid(tiles_x * tiles_y, nu);
+            #define NORM_ARGS acc4, accw, acc_i64, stats, sidx, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag
+            if (clean && det) k_normalise<true, true><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
+            else if (clean)   k_normalise<true, false><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
+            else              k_normalise<false, true><<<grid, TILE_THREADS, 0, st>>>(NORM_ARGS);
+            #undef NORM_ARGS
+        }
         prof_end(ctx, st);
         LAUNCH_CHECK("k_normalise");
     }
