@@ -27,7 +27,8 @@ def nvcc_path() -> str:
 
 
 def build_library(force: bool = False, verbose: bool = False) -> str:
-    deps = [SRC, os.path.join(INC, "tcwarp.h")]
+    csrc = os.path.dirname(SRC)
+    deps = [os.path.join(csrc, f) for f in os.listdir(csrc) if f.endswith((".cu", ".cuh"))] + [os.path.join(INC, "tcwarp.h")]
     if not force and os.path.exists(LIB) and all(os.path.getmtime(LIB) >= os.path.getmtime(d) for d in deps):
         return LIB
     cmd = [nvcc_path(), *NVCC_FLAGS, "-I", INC, "-o", LIB, SRC]

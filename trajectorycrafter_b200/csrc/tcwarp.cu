@@ -42,8 +42,14 @@ struct tcw_ctx {
     int pipeline_off;           // TCW_NO_PIPELINE env: use the per-chunk launches for the fp32 path too
     int pipe_lag_override;      // TCW_PIPE_LAG env (0 = auto)
     int pipe_blocks;            // resident CTAs of k_warp_pipeline on this device (0 = not queried yet)
+    int pipe2_blocks;           // resident CTAs of k_warp_pipeline2 (0 = not queried yet)
+    int use_v3;                 // TCW_V3 env: keep the one-pixel-per-lane kernels (warp_strip.cuh) for A/B runs
     // resources of the host-buffer entry point (grow-only)
     cudaStream_t s_in, s_run, s_out;
+    cudaStream_t s_aux;         // second stream of the two-stream fp32 path (normalise of chunk k under splat of chunk k+1)
+    cudaEvent_t ev_splat[2], ev_norm[2];
+    int serial;                 // TCW_SERIAL env: two-stream path on the caller's stream only (A/B measurement)
+    int persist;                // TCW_PERSIST env: use the single persistent kernel (warp_pipeline2.cuh) instead
     void* pool;
     size_t pool_bytes;
     // optional per-kernel timing (tcw_profile_*): event pairs around every launch
@@ -126,6 +132,12 @@ TCW_API int tcw_create(int device, tcw_ctx** out) {
     c->pipeline_off = env ? atoi(env) : 0;
     env = getenv("TCW_PIPE_LAG");
     c->pipe_lag_override = env ? atoi(env) : 0;
+    env = getenv("TCW_V3");
+    c->use_v3 = env ? atoi(env) : 0;
+    env = getenv("TCW_SERIAL");
+    c->serial = env ? atoi(env) : 0;
+    env = getenv("TCW_PERSIST");
+    c->persist = env ? atoi(env) : 0;
     *out = c;
     return TCW_OK;
 }
@@ -141,6 +153,10 @@ TCW_API void tcw_destroy(tcw_ctx* c) {
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_run) cudaStreamDestroy(c->s_run);
     if (c->s_out) cudaStreamDestroy(c->s_out);
+    if (c->s_aux) {
+        cudaStreamDestroy(c->s_aux);
+        for (int i = 0; i < 2; ++i) { cudaEventDestroy(c->ev_splat[i]); cudaEventDestroy(c->ev_norm[i]); }
+    }
     cudaSetDevice(prev);
     free(c);
 }
@@ -228,6 +244,8 @@ __device__ __forceinline__ float block_max_256(float v) {
 #include "warp_fast.cuh"
 #include "warp_strip.cuh"
 #include "warp_pipeline.cuh"
+#include "warp_pair.cuh"
+#include "warp_pipeline2.cuh"
 
 // ----------------------------------------------------------------------------------------------
 // compute_transformed_points as a standalone op
@@ -374,7 +392,11 @@ TCW_API int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, i
     if (!ctx || !bytes || n_units <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_workspace_bytes: bad argument");
     const size_t per_px = acc_bytes_per_px(flags);
     int g = auto_chunk_units(ctx, n_units, h, w, per_px);
-    if (!(flags & (TCW_DETERMINISTIC | TCW_CLEAN)) && g < PIPE_RING) g = PIPE_RING;   // accumulator ring of the pipeline kernel
+    int ring_max = PIPE_RING > PIPE2_RING ? PIPE_RING : PIPE2_RING;                   // accumulator ring of the pipeline kernels
+    if (ring_max < 16) ring_max = 16;                                                 // two buffers of 8 units (two-stream path)
+    if (ring_max < 2 * ctx->chunk_units_override) ring_max = 2 * ctx->chunk_units_override;
+    if (ring_max > 2 * n_units) ring_max = 2 * n_units;
+    if (!(flags & (TCW_DETERMINISTIC | TCW_CLEAN)) && g < ring_max) g = ring_max;
     *bytes = header_bytes(n_units) + align_up((size_t)g * per_px * h * w, 256);
     return TCW_OK;
 }
@@ -404,6 +426,7 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     cudaStream_t st = (cudaStream_t)cuda_stream;
     int g = (int)((workspace_bytes - hdr) / unit_bytes);
     const bool ring_fits = g >= PIPE_RING;
+    const bool ring2_fits = g >= PIPE2_RING;
     const int want = auto_chunk_units(ctx, n_units, h, w, acc_bytes_per_px(flags));
     if (g > want) g = want;
     UnitStats* stats = (UnitStats*)((char*)workspace + CTRL_BYTES);
@@ -422,6 +445,10 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     const bool per_unit = flags & TCW_PER_UNIT_MAX;
     const bool clean = flags & TCW_CLEAN;
     const int sidx = per_unit ? -1 : n_units;
+    // v4 (two pixels per lane, warp-granular pipeline) serves the plain fp32 path; the other modes keep warp_strip.cuh
+    const bool rezero = !det && !clean;
+    const bool use_v4 = rezero && ctx->persist && !ctx->use_v3 && !ctx->pipeline_off && ring2_fits && hw < 0x7fffffffull / 4;
+    const bool pair_chunk = rezero && !ctx->use_v3 && !use_v4 && hw < 0x7fffffffull / 4;   // v4 strip code, per-chunk launches
     CUDA_TRY(cudaMemsetAsync(workspace, 0, hdr, st));   // ticket + per-unit stats and counters
     {   // K0: soft-z normaliser of every unit (and of the whole call) before any splat
         const int quads = h * ((w + 3) / 4);
@@ -430,19 +457,116 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         for (int u0 = 0; u0 < n_units; u0 += 65535) {
             const int nu = n_units - u0 < 65535 ? n_units - u0 : 65535;
             prof_begin(ctx, PK_ZMAX, nu, st);
-            k_zmax_quad<<<dim3(bx, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, stats, n_units);
+            k_zmax_quad<<<dim3(bx, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, stats, n_units, (use_v4 || pair_chunk) ? 1 : 0);
             prof_end(ctx, st);
             LAUNCH_CHECK("k_zmax_quad");
         }
     }
     // the plain fp32 normalise kernel re-zeroes what it read: one memset per call instead of one per chunk
-    const bool rezero = !det && !clean;
     const bool vec = (hw % 4 == 0) && ((((size_t)accbase) | ((size_t)out_frame) | ((size_t)out_mask) | ((size_t)out_depth)) % 16 == 0);
     SplatArgs A;
     A.frame = frame; A.mask1 = mask1; A.depth = depth; A.src_index = src_index; A.Mall = M;
     A.h = h; A.w = w; A.strips_x = strips_x; A.strips_per_unit = strips_per_unit;
     A.stats = stats; A.stat_index_global = sidx;
     A.acc4 = acc4; A.accw = accw; A.acc_i64 = acc_i64; A.wmax = wmax; A.det_scale = det_scale; A.out_flow = out_flow;
+    if (pair_chunk && !ctx->pipeline_off) {
+        // fp32 path: chunks of g2 units, two accumulator buffers; the splat of chunk k+1 (issue-bound) runs on the
+        // caller's stream while the normalise of chunk k (memory-bound) runs on an internal second stream
+        if (!ctx->s_aux) {
+            CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_aux, cudaStreamNonBlocking));
+            for (int i = 0; i < 2; ++i) {
+                CUDA_TRY(cudaEventCreateWithFlags(&ctx->ev_splat[i], cudaEventDisableTiming));
+                CUDA_TRY(cudaEventCreateWithFlags(&ctx->ev_norm[i], cudaEventDisableTiming));
+            }
+        }
+        const int cap = (int)((workspace_bytes - hdr) / unit_bytes);          // units the workspace can hold
+        int g2 = ctx->chunk_units_override > 0 ? ctx->chunk_units_override : 8;
+        if (g2 > cap / 2) g2 = cap / 2;
+        if (g2 >= 1) {
+            if (g2 > n_units) g2 = n_units;
+            PairArgs B;
+            B.frame = frame; B.mask1 = mask1; B.depth = depth; B.src_index = src_index; B.Mall = M;
+            B.h = h; B.w = w; B.strips_x = (w + PAIR_W - 1) / PAIR_W;
+            B.strips_per_unit = B.strips_x * ((h + PAIR_H_CHUNK - 1) / PAIR_H_CHUNK);
+            B.stats = stats; B.stat_index_global = sidx; B.out_flow = out_flow;
+            const int pb = (B.strips_per_unit + PIPE2_THREADS / 32 - 1) / (PIPE2_THREADS / 32);
+            // buffer b: [g2][hw] float4 then [g2][hw] float
+            const size_t buf_bytes = (size_t)g2 * NCH * hw * sizeof(float);
+            CUDA_TRY(cudaMemsetAsync(accbase, 0, 2 * buf_bytes, st));
+            int k = 0;
+            for (int u0 = 0; u0 < n_units; u0 += g2, ++k) {
+                const int nu = n_units - u0 < g2 ? n_units - u0 : g2, b = k & 1;
+                char* buf = accbase + (size_t)b * buf_bytes;
+                B.acc4 = (float4*)buf;
+                B.accw = (float*)(buf + (size_t)g2 * hw * sizeof(float4));
+                cudaStream_t sn = ctx->serial ? st : ctx->s_aux;
+                if (k >= 2 && !ctx->serial) CUDA_TRY(cudaStreamWaitEvent(st, ctx->ev_norm[b], 0));      // buffer b normalised + re-zeroed
+                prof_begin(ctx, PK_SPLAT, nu, st);
+                k_splat_pair<<<dim3(pb, nu), PIPE2_THREADS, 0, st>>>(B, u0);
+                prof_end(ctx, st);
+                LAUNCH_CHECK("k_splat_pair");
+                if (!ctx->serial) {
+                    CUDA_TRY(cudaEventRecord(ctx->ev_splat[b], st));
+                    CUDA_TRY(cudaStreamWaitEvent(sn, ctx->ev_splat[b], 0));
+                }
+                prof_begin(ctx, PK_NORMALISE, nu, sn);
+                k_normalise_pair<<<dim3((unsigned)((hw + 1023) / 1024), nu), 256, 0, sn>>>(
+                    B.acc4, B.accw, u0, hw, (float*)out_frame, (float*)out_mask, out_depth, range_flag);
+                prof_end(ctx, sn);
+                LAUNCH_CHECK("k_normalise_pair");
+                if (!ctx->serial) CUDA_TRY(cudaEventRecord(ctx->ev_norm[b], sn));
+            }
+            // join: the caller's stream continues only after the last normalise of either buffer
+            if (!ctx->serial) {
+                CUDA_TRY(cudaStreamWaitEvent(st, ctx->ev_norm[(k - 1) & 1], 0));
+                if (k >= 2) CUDA_TRY(cudaStreamWaitEvent(st, ctx->ev_norm[k & 1], 0));
+            }
+            return TCW_OK;
+        }
+    }
+    if (use_v4) {
+        // fp32 path: one persistent kernel, warp-granular items (warp_pipeline2.cuh)
+        if (!ctx->pipe2_blocks) {
+            int per_sm = 0;
+            CUDA_TRY(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_warp_pipeline2, PIPE2_THREADS, 0));
+            ctx->pipe2_blocks = (per_sm > 0 ? per_sm : 1) * ctx->sm_count;
+        }
+        Pipe2Args P;
+        P.A.frame = frame; P.A.mask1 = mask1; P.A.depth = depth; P.A.src_index = src_index; P.A.Mall = M;
+        P.A.h = h; P.A.w = w; P.A.strips_x = (w + PAIR_W - 1) / PAIR_W;
+        P.A.strips_per_unit = P.A.strips_x * ((h + PAIR_H - 1) / PAIR_H);
+        P.A.stats = stats; P.A.stat_index_global = sidx;
+        // ring layout: [PIPE2_RING][hw] float4 then [PIPE2_RING][hw] float
+        P.A.acc4 = (float4*)accbase;
+        P.A.accw = (float*)(accbase + (size_t)PIPE2_RING * hw * sizeof(float4));
+        P.A.out_flow = out_flow;
+        CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)PIPE2_RING * NCH * hw * sizeof(float), st));
+        P.stats_rw = stats; P.ticket = ticket;
+        { const char* dg = getenv("TCW_DIAG"); P.diag = dg ? atoi(dg) : 0; }
+        P.n_units = n_units; P.ns = P.A.strips_per_unit; P.vec = vec ? 1 : 0;
+        P.nn = (int)(((vec ? hw / 4 : hw) + NORM2_QUADS - 1) / NORM2_QUADS);
+        P.out_frame = (float*)out_frame; P.out_mask = (float*)out_mask; P.out_depth = out_depth; P.range_flag = range_flag;
+        const long long total_s = (long long)n_units * P.ns, total_n = (long long)n_units * P.nn;
+        if (total_s + total_n > 0x7fffff00ll) return fail(TCW_E_ARG, "tcw_forward_warp: too many work items for one call");
+        const long long most = total_s > total_n ? total_s : total_n;
+        const long long want_blocks = (most + PIPE2_THREADS / 32 - 1) / (PIPE2_THREADS / 32);
+        const int blocks = (long long)ctx->pipe2_blocks < want_blocks ? ctx->pipe2_blocks : (int)want_blocks;
+        {   // ring: a unit stays in the ring for about two strip times (its strips run, then its owners pick the
+            // normalise items up after their next strip); the grid starts warps / ns units per strip time
+            const int warps = blocks * (PIPE2_THREADS / 32);
+            int ring = (int)((2.2 * warps) / P.ns) + 3;
+            if (ctx->pipe_lag_override > 0) ring = ctx->pipe_lag_override + 2;
+            if (ring < 2) ring = 2;
+            if (ring > PIPE2_RING) ring = PIPE2_RING;
+            P.lag = ring - 2; P.ring = ring;
+        }
+        prof_begin(ctx, PK_SPLAT, n_units, st);
+        void* kargs[] = {&P};      // cooperative: the static schedule needs every warp of the grid resident
+        CUDA_TRY(cudaLaunchCooperativeKernel((const void*)k_warp_pipeline2, dim3(blocks), dim3(PIPE2_THREADS), kargs, 0, st));
+        prof_end(ctx, st);
+        LAUNCH_CHECK("k_warp_pipeline2");
+        return TCW_OK;
+    }
     if (rezero && !ctx->pipeline_off && ring_fits) {
         // fp32 path: one persistent kernel runs splat + normalise of every unit (warp_pipeline.cuh)
         if (!ctx->pipe_blocks) {
@@ -495,7 +619,17 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         } else {
             if (!rezero) CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)g * NCH * hw * sizeof(float), st));
             prof_begin(ctx, PK_SPLAT, nu, st);
-            k_splat_strip<MODE_F32><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
+            if (pair_chunk) {
+                PairArgs B;
+                B.frame = frame; B.mask1 = mask1; B.depth = depth; B.src_index = src_index; B.Mall = M;
+                B.h = h; B.w = w; B.strips_x = (w + PAIR_W - 1) / PAIR_W;
+                B.strips_per_unit = B.strips_x * ((h + PAIR_H_CHUNK - 1) / PAIR_H_CHUNK);
+                B.stats = stats; B.stat_index_global = sidx; B.acc4 = acc4; B.accw = accw; B.out_flow = out_flow;
+                const int pb = (B.strips_per_unit + PIPE2_THREADS / 32 - 1) / (PIPE2_THREADS / 32);
+                k_splat_pair<<<dim3(pb, nu), PIPE2_THREADS, 0, st>>>(B, u0);
+            } else {
+                k_splat_strip<MODE_F32><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
+            }
             prof_end(ctx, st);
             LAUNCH_CHECK("k_splat_strip<f32>");
         }

@@ -31,9 +31,11 @@ __device__ __forceinline__ float project_z(const float* M, bool simple, float fx
     return Y2 <= 0.01f ? 1000.0f : P2;
 }
 
+__device__ float log1x_fwd(float a);      // warp_pair.cuh
+
 __global__ void __launch_bounds__(TILE_THREADS)
 k_zmax_quad(const float* __restrict__ depth, const int* __restrict__ src_index, const float* __restrict__ Mall,
-            int unit0, int h, int w, UnitStats* __restrict__ stats, int n_units_total) {
+            int unit0, int h, int w, UnitStats* __restrict__ stats, int n_units_total, int poly_log) {
     __shared__ float M[M_FLOATS];
     const int u = unit0 + blockIdx.y;
     if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
@@ -63,7 +65,9 @@ k_zmax_quad(const float* __restrict__ depth, const int* __restrict__ src_index, 
             }
         }
     }
-    const float ld = logf(__fadd_rn(1.0f, zs));      // == max over pixels of log(1+sat(z')): logf is monotone
+    // == max over pixels of log(1+sat(z')): log is monotone.  poly_log: the same polynomial the v4 splat kernel
+    // evaluates per pixel (warp_pair.cuh log2x), so that ld / L is exactly 1 at the arg-max pixel
+    const float ld = poly_log ? log1x_fwd(__fadd_rn(1.0f, zs)) : logf(__fadd_rn(1.0f, zs));
     const float m = block_max_256(ld);
     __syncthreads();
     const float mz = block_max_256(za);

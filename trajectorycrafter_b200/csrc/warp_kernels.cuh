@@ -13,6 +13,8 @@ struct UnitStats {
     unsigned zabs;     // max |z'| (scale of the fixed-point depth channel)
     int splat_done;    // pipeline kernel: splat items of this unit that have finished
     int norm_done;     // pipeline kernel: normalise items of this unit that have finished
+    int splat_claim;   // pipeline kernel v4: splat items of this unit handed out so far
+    int norm_claim;    // pipeline kernel v4: normalise items of this unit handed out so far
 };
 
 // block-wide sum of NV values held by every thread; result valid in thread 0
