@@ -6,7 +6,7 @@ import os
 from ctypes import POINTER, c_char_p, c_double, c_float, c_int, c_longlong, c_size_t, c_void_p
 
 HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(HERE, "libtcwarp.so")
+LIB_PATH = os.environ.get("TCW_LIB", os.path.join(HERE, "libtcwarp.so"))   # TCW_LIB: A/B builds of the same library
 
 # flags (include/tcwarp.h)
 TCW_PER_UNIT_MAX = 1

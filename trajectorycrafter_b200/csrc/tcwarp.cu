@@ -48,7 +48,10 @@ struct tcw_ctx {
     cudaStream_t s_in, s_run, s_out;
     cudaStream_t s_aux;         // second stream of the two-stream fp32 path (normalise of chunk k under splat of chunk k+1)
     cudaEvent_t ev_splat[2], ev_norm[2];
-    int serial;                 // TCW_SERIAL env: two-stream path on the caller's stream only (A/B measurement)
+    cudaStream_t s_lane[7];     // extra streams of the multi-lane schedule (lane 0 is the caller's stream)
+    cudaEvent_t ev_lane[7];
+    int lanes;                  // TCW_LANES env (0 = default)
+    int serial;                 // TCW_SERIAL env: schedule of the chunked fp32 path (see tcw_create)
     int persist;                // TCW_PERSIST env: use the single persistent kernel (warp_pipeline2.cuh) instead
     void* pool;
     size_t pool_bytes;
@@ -134,8 +137,10 @@ TCW_API int tcw_create(int device, tcw_ctx** out) {
     c->pipe_lag_override = env ? atoi(env) : 0;
     env = getenv("TCW_V3");
     c->use_v3 = env ? atoi(env) : 0;
-    env = getenv("TCW_SERIAL");
-    c->serial = env ? atoi(env) : 0;
+    env = getenv("TCW_LANES");
+    c->lanes = env ? atoi(env) : 0;
+    env = getenv("TCW_SERIAL");     // 2 (default): independent lanes; 1: one stream; 0: splat stream + normalise stream
+    c->serial = env ? atoi(env) : 2;
     env = getenv("TCW_PERSIST");
     c->persist = env ? atoi(env) : 0;
     *out = c;
@@ -153,6 +158,7 @@ TCW_API void tcw_destroy(tcw_ctx* c) {
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_run) cudaStreamDestroy(c->s_run);
     if (c->s_out) cudaStreamDestroy(c->s_out);
+    for (int i = 0; i < 7; ++i) if (c->s_lane[i]) { cudaStreamDestroy(c->s_lane[i]); cudaEventDestroy(c->ev_lane[i]); }
     if (c->s_aux) {
         cudaStreamDestroy(c->s_aux);
         for (int i = 0; i < 2; ++i) { cudaEventDestroy(c->ev_splat[i]); cudaEventDestroy(c->ev_norm[i]); }
@@ -388,14 +394,38 @@ static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, size_
     return g < n_units ? g : n_units;
 }
 
+// lanes x units-per-chunk of the multi-stream fp32 path.  Units in flight = lanes * chunk: their accumulators
+// (20 B/px) should stay L2-resident next to the streaming traffic; measured optimum on B200 at 384x672:
+// 4 lanes x 4 units = 83 MB of the 126 MB L2 (profiles/r1_v4_notes.md).
+static void lanes_plan(const tcw_ctx* ctx, int n_units, size_t hw, int* lanes, int* chunk) {
+    int NL = ctx->lanes > 0 ? ctx->lanes : 4;
+    if (NL > 8) NL = 8;
+    int g2 = ctx->chunk_units_override;
+    if (g2 <= 0) {
+        const size_t l2 = ctx->l2_bytes ? ctx->l2_bytes : ((size_t)64 << 20);
+        int inflight = (int)((l2 * 2 / 3) / (hw * NCH * sizeof(float)));
+        if (inflight < 2) inflight = 2;
+        if (ctx->lanes <= 0 && NL > inflight) NL = inflight;
+        g2 = inflight / NL;
+        if (g2 < 1) g2 = 1;
+        if (g2 > 4096) g2 = 4096;
+    }
+    if (ctx->serial != 2) NL = 2;
+    const int per_lane = (n_units + NL - 1) / NL;
+    if (g2 > per_lane) g2 = per_lane;
+    *lanes = NL; *chunk = g2;
+}
+
 TCW_API int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, int flags, size_t* bytes) {
     if (!ctx || !bytes || n_units <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_workspace_bytes: bad argument");
     const size_t per_px = acc_bytes_per_px(flags);
     int g = auto_chunk_units(ctx, n_units, h, w, per_px);
     int ring_max = PIPE_RING > PIPE2_RING ? PIPE_RING : PIPE2_RING;                   // accumulator ring of the pipeline kernels
-    if (ring_max < 16) ring_max = 16;                                                 // two buffers of 8 units (two-stream path)
-    if (ring_max < 2 * ctx->chunk_units_override) ring_max = 2 * ctx->chunk_units_override;
-    if (ring_max > 2 * n_units) ring_max = 2 * n_units;
+    {   // lanes x chunk units of the multi-stream path
+        int nl = 1, g2 = 1;
+        lanes_plan(ctx, n_units, (size_t)h * w, &nl, &g2);
+        if (ring_max < nl * g2) ring_max = nl * g2;
+    }
     if (!(flags & (TCW_DETERMINISTIC | TCW_CLEAN)) && g < ring_max) g = ring_max;
     *bytes = header_bytes(n_units) + align_up((size_t)g * per_px * h * w, 256);
     return TCW_OK;
@@ -470,8 +500,7 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     A.stats = stats; A.stat_index_global = sidx;
     A.acc4 = acc4; A.accw = accw; A.acc_i64 = acc_i64; A.wmax = wmax; A.det_scale = det_scale; A.out_flow = out_flow;
     if (pair_chunk && !ctx->pipeline_off) {
-        // fp32 path: chunks of g2 units, two accumulator buffers; the splat of chunk k+1 (issue-bound) runs on the
-        // caller's stream while the normalise of chunk k (memory-bound) runs on an internal second stream
+        // fp32 path: chunks of g2 units, each with its own accumulator buffer, spread over NL streams ("lanes")
         if (!ctx->s_aux) {
             CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_aux, cudaStreamNonBlocking));
             for (int i = 0; i < 2; ++i) {
@@ -480,8 +509,10 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
             }
         }
         const int cap = (int)((workspace_bytes - hdr) / unit_bytes);          // units the workspace can hold
-        int g2 = ctx->chunk_units_override > 0 ? ctx->chunk_units_override : 8;
-        if (g2 > cap / 2) g2 = cap / 2;
+        int NL = 1, g2 = 1;
+        lanes_plan(ctx, n_units, hw, &NL, &g2);
+        if (NL > cap) NL = cap > 0 ? cap : 1;
+        if (g2 > cap / NL) g2 = cap / NL;
         if (g2 >= 1) {
             if (g2 > n_units) g2 = n_units;
             PairArgs B;
@@ -492,8 +523,40 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
             const int pb = (B.strips_per_unit + PIPE2_THREADS / 32 - 1) / (PIPE2_THREADS / 32);
             // buffer b: [g2][hw] float4 then [g2][hw] float
             const size_t buf_bytes = (size_t)g2 * NCH * hw * sizeof(float);
-            CUDA_TRY(cudaMemsetAsync(accbase, 0, 2 * buf_bytes, st));
+            if (ctx->serial != 2) CUDA_TRY(cudaMemsetAsync(accbase, 0, 2 * buf_bytes, st));
             int k = 0;
+            if (ctx->serial == 2) {
+                // independent lanes: chunk k runs splat + normalise on stream k % NL with buffer k % NL; the tail of
+                // one lane's kernel overlaps the other lanes' kernels, and nothing waits across lanes until the join
+                for (int i = 0; i + 1 < NL; ++i) if (!ctx->s_lane[i]) {
+                    CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_lane[i], cudaStreamNonBlocking));
+                    CUDA_TRY(cudaEventCreateWithFlags(&ctx->ev_lane[i], cudaEventDisableTiming));
+                }
+                CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)NL * buf_bytes, st));
+                CUDA_TRY(cudaEventRecord(ctx->ev_splat[0], st));
+                for (int i = 0; i + 1 < NL; ++i) CUDA_TRY(cudaStreamWaitEvent(ctx->s_lane[i], ctx->ev_splat[0], 0));
+                for (int u0 = 0; u0 < n_units; u0 += g2, ++k) {
+                    const int nu = n_units - u0 < g2 ? n_units - u0 : g2, b = k % NL;
+                    cudaStream_t sk = b ? ctx->s_lane[b - 1] : st;
+                    char* buf = accbase + (size_t)b * buf_bytes;
+                    B.acc4 = (float4*)buf;
+                    B.accw = (float*)(buf + (size_t)g2 * hw * sizeof(float4));
+                    prof_begin(ctx, PK_SPLAT, nu, sk);
+                    k_splat_pair<<<dim3(pb, nu), PIPE2_THREADS, 0, sk>>>(B, u0);
+                    prof_end(ctx, sk);
+                    LAUNCH_CHECK("k_splat_pair");
+                    prof_begin(ctx, PK_NORMALISE, nu, sk);
+                    k_normalise_pair<<<dim3((unsigned)((hw + 1023) / 1024), nu), 256, 0, sk>>>(
+                        B.acc4, B.accw, u0, hw, (float*)out_frame, (float*)out_mask, out_depth, range_flag);
+                    prof_end(ctx, sk);
+                    LAUNCH_CHECK("k_normalise_pair");
+                }
+                for (int i = 0; i + 1 < NL; ++i) {
+                    CUDA_TRY(cudaEventRecord(ctx->ev_lane[i], ctx->s_lane[i]));
+                    CUDA_TRY(cudaStreamWaitEvent(st, ctx->ev_lane[i], 0));
+                }
+                return TCW_OK;
+            }
             for (int u0 = 0; u0 < n_units; u0 += g2, ++k) {
                 const int nu = n_units - u0 < g2 ? n_units - u0 : g2, b = k & 1;
                 char* buf = accbase + (size_t)b * buf_bytes;

@@ -14,6 +14,9 @@
 constexpr int PIPE2_RING = 12;                  // accumulator slots the workspace provides (upper bound of ring)
 constexpr int NORM2_QUADS = 256;                // quads (VEC) or pixels (scalar) per normalise item
 constexpr int PIPE2_THREADS = 128;
+#ifndef TCW_SPLAT_MINB
+#define TCW_SPLAT_MINB 4          // resident CTAs per SM the splat kernels are register-capped for
+#endif
 
 struct Pipe2Args {
     PairArgs A;
@@ -109,7 +112,7 @@ k_warp_pipeline2(Pipe2Args P) {
 }
 
 // per-chunk launch of the same strip code (used when the ring does not fit the workspace, and by ncu studies)
-__global__ void __launch_bounds__(PIPE2_THREADS, 4)
+__global__ void __launch_bounds__(PIPE2_THREADS, TCW_SPLAT_MINB)
 k_splat_pair(PairArgs A, int unit0) {
     const int strip = blockIdx.x * (PIPE2_THREADS / 32) + (threadIdx.x >> 5);
     if (strip >= A.strips_per_unit) return;                          // whole warps leave together
