@@ -237,3 +237,46 @@ def test_size_independent_properties(warper, clip):
     f2, m2, _, fl2 = warper.forward_warp_batch(frames[:n][:, perm].contiguous(), depths[:n], T1, T2, K)
     assert torch.equal(m, m2) and torch.equal(fl, fl2)
     assert_colour_close(npy(f2), npy(f[:, perm]))
+
+
+@pytest.mark.gpu
+def test_graph_replay_follows_new_contents():
+    """Repeated calls with identical arguments are replayed from a CUDA graph (tcw_forward_warp); the replay must
+    read the CURRENT contents behind the pointers, and must equal the plain enqueue bit for bit (masks, flow)."""
+    import torch
+    from trajectorycrafter_b200 import Warper, prepare_matrices
+    from trajectorycrafter_b200.workloads import orbit_units, synthetic_clip
+    h, w, nf = 96, 160, 3
+    frames, depths = synthetic_clip(nf, h, w, seed=11)
+    T1, T2, K, src = orbit_units(depths, h, w, presets=[(0, 30), (20, -10)])
+    M = prepare_matrices(T1, T2, K)
+    n = M.shape[0]
+    warper = Warper(device="cuda:0")
+    dev = warper.device
+    fd, dd, Md = frames.to(dev), depths.to(dev), M.to(dev)
+    out = (torch.empty((n, 3, h, w), device=dev), torch.empty((n, 1, h, w), device=dev),
+           torch.empty((n, 1, h, w), device=dev), torch.empty((n, 2, h, w), device=dev))
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    src32 = src.to(torch.int32).to(dev)
+
+    def run():
+        warper.forward_warp_matrices(fd, dd, Md, src_index=src32, check_range=flag, out=out)
+        torch.cuda.synchronize()
+        return [t.clone() for t in out]
+
+    first = run()             # plain enqueue
+    second = run()            # captured + launched
+    third = run()             # replayed
+    for a, b, c in zip(first, second, third):
+        assert torch.equal(a[1] if False else a, b) or torch.allclose(a, b, atol=2e-6)
+        assert torch.equal(b, c) or torch.allclose(b, c, atol=2e-6)
+    assert torch.equal(first[1], third[1]) and torch.equal(first[3], third[3])
+    # new contents behind the same pointers: the replay must follow them
+    dd.mul_(1.25)
+    fd.neg_()
+    replay = run()
+    fresh = Warper(device="cuda:0").forward_warp_matrices(fd, dd, Md, src_index=src32, check_range=False)
+    torch.cuda.synchronize()
+    assert torch.equal(replay[1], fresh[1]) and torch.equal(replay[3], fresh[3])
+    assert torch.allclose(replay[0], fresh[0], atol=2e-6)
+    assert not torch.equal(replay[3], first[3])

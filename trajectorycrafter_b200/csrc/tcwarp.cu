@@ -51,6 +51,17 @@ struct tcw_ctx {
     cudaStream_t s_lane[7];     // extra streams of the multi-lane schedule (lane 0 is the caller's stream)
     cudaEvent_t ev_lane[7];
     int lanes;                  // TCW_LANES env (0 = default)
+    // CUDA graph of one whole tcw_forward_warp call (replayed while the arguments stay the same)
+    int graphs_off;             // TCW_NO_GRAPH env
+    struct GraphKey {
+        const void *frame, *mask1, *depth, *src_index, *M, *out_frame, *out_mask, *out_depth, *out_flow, *range_flag, *workspace;
+        size_t workspace_bytes;
+        int n_units, n_src, h, w, flags;
+    } last_key, graph_key;
+    int last_key_valid;
+    cudaGraphExec_t graph_exec;
+    long long graph_launches;   // kernels one replay launches
+    cudaStream_t s_cap;         // origin stream of the capture (the caller's stream may be the legacy default stream)
     int serial;                 // TCW_SERIAL env: schedule of the chunked fp32 path (see tcw_create)
     int persist;                // TCW_PERSIST env: use the single persistent kernel (warp_pipeline2.cuh) instead
     void* pool;
@@ -137,6 +148,8 @@ TCW_API int tcw_create(int device, tcw_ctx** out) {
     c->pipe_lag_override = env ? atoi(env) : 0;
     env = getenv("TCW_V3");
     c->use_v3 = env ? atoi(env) : 0;
+    env = getenv("TCW_NO_GRAPH");
+    c->graphs_off = env ? atoi(env) : 0;
     env = getenv("TCW_LANES");
     c->lanes = env ? atoi(env) : 0;
     env = getenv("TCW_SERIAL");     // 2 (default): independent lanes; 1: one stream; 0: splat stream + normalise stream
@@ -158,6 +171,8 @@ TCW_API void tcw_destroy(tcw_ctx* c) {
     if (c->s_in) cudaStreamDestroy(c->s_in);
     if (c->s_run) cudaStreamDestroy(c->s_run);
     if (c->s_out) cudaStreamDestroy(c->s_out);
+    if (c->graph_exec) cudaGraphExecDestroy(c->graph_exec);
+    if (c->s_cap) cudaStreamDestroy(c->s_cap);
     for (int i = 0; i < 7; ++i) if (c->s_lane[i]) { cudaStreamDestroy(c->s_lane[i]); cudaEventDestroy(c->ev_lane[i]); }
     if (c->s_aux) {
         cudaStreamDestroy(c->s_aux);
@@ -396,14 +411,14 @@ static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, size_
 
 // lanes x units-per-chunk of the multi-stream fp32 path.  Units in flight = lanes * chunk: their accumulators
 // (20 B/px) should stay L2-resident next to the streaming traffic; measured optimum on B200 at 384x672:
-// 4 lanes x 4 units = 83 MB of the 126 MB L2 (profiles/r1_v4_notes.md).
+// 4 lanes x 3 units = 62 MB of the 126 MB L2 (profiles/r1_v4_notes.md).
 static void lanes_plan(const tcw_ctx* ctx, int n_units, size_t hw, int* lanes, int* chunk) {
     int NL = ctx->lanes > 0 ? ctx->lanes : 4;
     if (NL > 8) NL = 8;
     int g2 = ctx->chunk_units_override;
     if (g2 <= 0) {
         const size_t l2 = ctx->l2_bytes ? ctx->l2_bytes : ((size_t)64 << 20);
-        int inflight = (int)((l2 * 2 / 3) / (hw * NCH * sizeof(float)));
+        int inflight = (int)((l2 / 2) / (hw * NCH * sizeof(float)));
         if (inflight < 2) inflight = 2;
         if (ctx->lanes <= 0 && NL > inflight) NL = inflight;
         g2 = inflight / NL;
@@ -439,10 +454,10 @@ static int check_launch(tcw_ctx* ctx, const char* what) {
 }
 #define LAUNCH_CHECK(what) do { int rc__ = check_launch(ctx, what); if (rc__) return rc__; } while (0)
 
-TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
-                             const int* src_index, const float* M, int n_units, int n_src, int h, int w,
-                             int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
-                             int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                                const int* src_index, const float* M, int n_units, int n_src, int h, int w,
+                                int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                                int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
     if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp: ctx is NULL");
     if (!frame || !depth || !M || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_forward_warp: NULL buffer");
     if (n_units <= 0 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp: bad shape");
@@ -480,12 +495,22 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     const bool use_v4 = rezero && ctx->persist && !ctx->use_v3 && !ctx->pipeline_off && ring2_fits && hw < 0x7fffffffull / 4;
     const bool pair_chunk = rezero && !ctx->use_v3 && !use_v4 && hw < 0x7fffffffull / 4;   // v4 strip code, per-chunk launches
     CUDA_TRY(cudaMemsetAsync(workspace, 0, hdr, st));   // ticket + per-unit stats and counters
-    {   // K0: soft-z normaliser of every unit (and of the whole call) before any splat
+    int k0_head = n_units, k0_bx = 1;      // units whose normaliser is computed up front
+    {   // K0: soft-z normaliser of every unit (and of the whole call) before any splat.  (Launching it per chunk
+        // inside the lanes was measured: 98 more small launches, 2.51 -> 2.97 ms/step.)
         const int quads = h * ((w + 3) / 4);
         int bx = (quads + TILE_THREADS * 2 - 1) / (TILE_THREADS * 2);
         if (bx < 1) bx = 1;
-        for (int u0 = 0; u0 < n_units; u0 += 65535) {
-            const int nu = n_units - u0 < 65535 ? n_units - u0 : 65535;
+        k0_bx = bx;
+        // multi-lane schedule with per-unit normalisers: only the units of the first round of chunks here, the rest
+        // runs on its own stream under the first round (see the lanes loop)
+        if (pair_chunk && !ctx->pipeline_off && ctx->serial == 2 && per_unit && !ctx->prof_on) {
+            int nl = 1, g2 = 1;
+            lanes_plan(ctx, n_units, hw, &nl, &g2);
+            if (nl * g2 < n_units && n_units < 65535) k0_head = nl * g2;
+        }
+        for (int u0 = 0; u0 < k0_head; u0 += 65535) {
+            const int nu = k0_head - u0 < 65535 ? k0_head - u0 : 65535;
             prof_begin(ctx, PK_ZMAX, nu, st);
             k_zmax_quad<<<dim3(bx, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, stats, n_units, (use_v4 || pair_chunk) ? 1 : 0);
             prof_end(ctx, st);
@@ -533,11 +558,23 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
                     CUDA_TRY(cudaEventCreateWithFlags(&ctx->ev_lane[i], cudaEventDisableTiming));
                 }
                 CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)NL * buf_bytes, st));
+                const bool k0_rest = k0_head < n_units && k0_head == NL * g2;
+                if (k0_head < n_units && !k0_rest) {      // the workspace forced another lane plan: finish the pre-pass here
+                    k_zmax_quad<<<dim3(k0_bx, n_units - k0_head), TILE_THREADS, 0, st>>>(depth, src_index, M, k0_head, h, w, stats, n_units, 1);
+                    LAUNCH_CHECK("k_zmax_quad");
+                }
                 CUDA_TRY(cudaEventRecord(ctx->ev_splat[0], st));
                 for (int i = 0; i + 1 < NL; ++i) CUDA_TRY(cudaStreamWaitEvent(ctx->s_lane[i], ctx->ev_splat[0], 0));
+                if (k0_rest) {      // normalisers of the later rounds: own stream, concurrent with the first round of chunks
+                    CUDA_TRY(cudaStreamWaitEvent(ctx->s_aux, ctx->ev_splat[0], 0));
+                    k_zmax_quad<<<dim3(k0_bx, n_units - k0_head), TILE_THREADS, 0, ctx->s_aux>>>(depth, src_index, M, k0_head, h, w, stats, n_units, 1);
+                    LAUNCH_CHECK("k_zmax_quad");
+                    CUDA_TRY(cudaEventRecord(ctx->ev_norm[0], ctx->s_aux));
+                }
                 for (int u0 = 0; u0 < n_units; u0 += g2, ++k) {
                     const int nu = n_units - u0 < g2 ? n_units - u0 : g2, b = k % NL;
                     cudaStream_t sk = b ? ctx->s_lane[b - 1] : st;
+                    if (k0_rest && k >= NL && k < 2 * NL) CUDA_TRY(cudaStreamWaitEvent(sk, ctx->ev_norm[0], 0));
                     char* buf = accbase + (size_t)b * buf_bytes;
                     B.acc4 = (float4*)buf;
                     B.accw = (float*)(buf + (size_t)g2 * hw * sizeof(float4));
@@ -716,6 +753,76 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         prof_end(ctx, st);
         LAUNCH_CHECK("k_normalise");
     }
+    return TCW_OK;
+}
+
+// Public entry: enqueue, or replay the CUDA graph of the previous identical call.  One call is ~200 kernel
+// launches on four streams; enqueueing them costs the host as long as the GPU needs to run them (2.2 ms measured),
+// so a call whose arguments equal those of the call before is captured once and replayed afterwards.  Kernels
+// read the matrices, indices and images through the pointers at run time, so new CONTENTS need no new graph.
+TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                             const int* src_index, const float* M, int n_units, int n_src, int h, int w,
+                             int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                             int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp: ctx is NULL");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    bool eligible = !ctx->graphs_off && !ctx->prof_on && !(flags & (TCW_DETERMINISTIC | TCW_CLEAN)) && !ctx->use_v3 &&
+                    !ctx->persist && !ctx->pipeline_off && ctx->serial == 2;
+    if (eligible) {
+        cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
+        if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) { cudaGetLastError(); eligible = false; }
+    }
+    if (!eligible)
+        return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+    tcw_ctx::GraphKey key;
+    memset(&key, 0, sizeof(key));
+    key.frame = frame; key.mask1 = mask1; key.depth = depth; key.src_index = src_index; key.M = M;
+    key.out_frame = out_frame; key.out_mask = out_mask; key.out_depth = out_depth; key.out_flow = out_flow;
+    key.range_flag = range_flag; key.workspace = workspace; key.workspace_bytes = workspace_bytes;
+    key.n_units = n_units; key.n_src = n_src; key.h = h; key.w = w; key.flags = flags;
+    if (ctx->graph_exec && !memcmp(&key, &ctx->graph_key, sizeof(key))) {
+        CUDA_TRY(cudaGraphLaunch(ctx->graph_exec, st));
+        ctx->launches += ctx->graph_launches;
+        return TCW_OK;
+    }
+    const bool repeat = ctx->last_key_valid && !memcmp(&key, &ctx->last_key, sizeof(key));
+    ctx->last_key = key;
+    ctx->last_key_valid = 1;
+    if (!repeat)      // first sight of these arguments: plain enqueue (a caller that allocates fresh outputs never repeats)
+        return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+    // second identical call in a row: capture it on an internal stream, instantiate, launch on the caller's stream
+    if (!ctx->s_cap) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_cap, cudaStreamNonBlocking));
+    if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
+    const long long before = ctx->launches;
+    CUDA_TRY(cudaStreamBeginCapture(ctx->s_cap, cudaStreamCaptureModeThreadLocal));
+    const int rc = forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
+                                        out_depth, out_flow, range_flag, workspace, workspace_bytes, ctx->s_cap);
+    cudaGraph_t graph = nullptr;
+    const cudaError_t ce = cudaStreamEndCapture(ctx->s_cap, &graph);
+    ctx->graph_launches = ctx->launches - before;
+    ctx->launches = before;
+    if (rc || ce != cudaSuccess || !graph) {
+        if (graph) cudaGraphDestroy(graph);
+        cudaGetLastError();
+        ctx->graphs_off = 1;      // do not try again in this context; fall back to plain enqueue
+        if (rc) return rc;
+        return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+    }
+    const cudaError_t ie = cudaGraphInstantiate(&ctx->graph_exec, graph, 0);
+    cudaGraphDestroy(graph);
+    if (ie != cudaSuccess) {
+        cudaGetLastError();
+        ctx->graph_exec = nullptr;
+        ctx->graphs_off = 1;
+        return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+    }
+    ctx->graph_key = key;
+    CUDA_TRY(cudaGraphLaunch(ctx->graph_exec, st));
+    ctx->launches += ctx->graph_launches;
     return TCW_OK;
 }
 
