@@ -232,6 +232,7 @@ def run_ours(args):
     def profile_pass(env):
         os.environ.update(env)
         w2 = Warper(device=f"cuda:{local}")
+        w2._context()              # tcw_create reads the TCW_* switches
         for k in env:
             os.environ.pop(k)
 

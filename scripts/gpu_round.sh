@@ -6,11 +6,11 @@ nvidia-smi --query-gpu=name,clocks.max.sm,clocks.sm,power.limit --format=csv > $
 timeout 900 python -m pytest tests -x -q -m gpu > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 $O/pytest_gpu.log
 timeout 600 python bench.py --steps 20 --warmup 3 > $O/bench.json 2> $O/bench.err; echo "bench rc=$?"; cat $O/bench.json
 timeout 300 python bench.py --steps 20 --warmup 3 --deterministic --no-e2e --no-cpu-baseline > $O/bench_det.json 2>> $O/bench.err; cat $O/bench_det.json
-TCW_NO_PIPELINE=1 timeout 300 python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline > $O/bench_chunk.json 2>> $O/bench.err; cat $O/bench_chunk.json
 timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > $O/bench_ref.json 2>> $O/bench.err; cat $O/bench_ref.json
+python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; tail -1 $O/smoke.log
 B="python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline"
 timeout 300 $B > $O/plain.log 2>&1 && \
-timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -c 400 --csv --log-file $O/launches.csv $B > $O/ncu1.log 2>&1
-timeout 900 ncu --set full --clock-control none --cache-control none --import-source on -k regex:k_warp_pipeline -s 3 -c 1 -o $O/pipeline_full $B > $O/ncu2.log 2>&1
-TCW_NO_PIPELINE=1 timeout 900 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"k_splat_strip|k_normalise_quad|k_zmax" -s 30 -c 3 -o $O/chunk_full $B > $O/ncu3.log 2>&1
+timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 800 -c 420 --csv --log-file $O/launches.csv $B > $O/ncu1.log 2>&1
+timeout 900 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"k_splat_pair|k_normalise_pair|k_zmax_quad" -s 60 -c 3 -o $O/kernels_full $B > $O/ncu2.log 2>&1
+TCW_SERIAL=1 TCW_CHUNK_UNITS=24 timeout 900 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"k_splat_pair|k_normalise_pair" -s 12 -c 2 -o $O/kernels_full_24units $B > $O/ncu3.log 2>&1
 ls -la $O

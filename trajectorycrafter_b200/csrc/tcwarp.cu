@@ -493,7 +493,8 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
     // v4 (two pixels per lane, warp-granular pipeline) serves the plain fp32 path; the other modes keep warp_strip.cuh
     const bool rezero = !det && !clean;
     const bool use_v4 = rezero && ctx->persist && !ctx->use_v3 && !ctx->pipeline_off && ring2_fits && hw < 0x7fffffffull / 4;
-    const bool pair_chunk = rezero && !ctx->use_v3 && !use_v4 && hw < 0x7fffffffull / 4;   // v4 strip code, per-chunk launches
+    const bool pair_ok = !ctx->use_v3 && hw < 0x7fffffffull / 4;                           // v4 strip code (warp_pair.cuh) usable
+    const bool pair_chunk = rezero && pair_ok && !use_v4;                                  // ... in per-chunk launches, fp32 path
     CUDA_TRY(cudaMemsetAsync(workspace, 0, hdr, st));   // ticket + per-unit stats and counters
     int k0_head = n_units, k0_bx = 1;      // units whose normaliser is computed up front
     {   // K0: soft-z normaliser of every unit (and of the whole call) before any splat.  (Launching it per chunk
@@ -512,7 +513,7 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
         for (int u0 = 0; u0 < k0_head; u0 += 65535) {
             const int nu = k0_head - u0 < 65535 ? k0_head - u0 : 65535;
             prof_begin(ctx, PK_ZMAX, nu, st);
-            k_zmax_quad<<<dim3(bx, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, stats, n_units, (use_v4 || pair_chunk) ? 1 : 0);
+            k_zmax_quad<<<dim3(bx, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, h, w, stats, n_units, (use_v4 || pair_ok) ? 1 : 0);
             prof_end(ctx, st);
             LAUNCH_CHECK("k_zmax_quad");
         }
@@ -703,35 +704,35 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
     for (int u0 = 0; u0 < n_units; u0 += g) {
         const int nu = n_units - u0 < g ? n_units - u0 : g;
         const dim3 sgrid(strip_blocks, nu);
+        PairArgs B;
+        B.frame = frame; B.mask1 = mask1; B.depth = depth; B.src_index = src_index; B.Mall = M;
+        B.h = h; B.w = w; B.strips_x = (w + PAIR_W - 1) / PAIR_W;
+        B.strips_per_unit = B.strips_x * ((h + PAIR_H_CHUNK - 1) / PAIR_H_CHUNK);
+        B.stats = stats; B.stat_index_global = sidx; B.acc4 = acc4; B.accw = accw; B.out_flow = out_flow;
+        B.acc_i64 = acc_i64; B.wmax = wmax; B.det_scale = det_scale;
+        const dim3 pgrid((B.strips_per_unit + PIPE2_THREADS / 32 - 1) / (PIPE2_THREADS / 32), nu);
         if (det) {
             CUDA_TRY(cudaMemsetAsync(acc_i64, 0, (size_t)nu * NCH * hw * sizeof(long long), st));
             CUDA_TRY(cudaMemsetAsync(wmax, 0, (size_t)nu * hw * sizeof(unsigned), st));
             A.out_flow = nullptr;
             prof_begin(ctx, PK_WMAX, nu, st);
-            k_splat_strip<MODE_WMAX><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
+            if (pair_ok) k_splat_pair_det<MODE_WMAX><<<pgrid, PIPE2_THREADS, 0, st>>>(B, u0);
+            else k_splat_strip<MODE_WMAX><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
             prof_end(ctx, st);
-            LAUNCH_CHECK("k_splat_strip<wmax>");
+            LAUNCH_CHECK("k_splat<wmax>");
             A.out_flow = out_flow;
             prof_begin(ctx, PK_SPLAT, nu, st);
-            k_splat_strip<MODE_I64><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
+            if (pair_ok) k_splat_pair_det<MODE_I64><<<pgrid, PIPE2_THREADS, 0, st>>>(B, u0);
+            else k_splat_strip<MODE_I64><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
             prof_end(ctx, st);
-            LAUNCH_CHECK("k_splat_strip<i64>");
+            LAUNCH_CHECK("k_splat<i64>");
         } else {
             if (!rezero) CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)g * NCH * hw * sizeof(float), st));
             prof_begin(ctx, PK_SPLAT, nu, st);
-            if (pair_chunk) {
-                PairArgs B;
-                B.frame = frame; B.mask1 = mask1; B.depth = depth; B.src_index = src_index; B.Mall = M;
-                B.h = h; B.w = w; B.strips_x = (w + PAIR_W - 1) / PAIR_W;
-                B.strips_per_unit = B.strips_x * ((h + PAIR_H_CHUNK - 1) / PAIR_H_CHUNK);
-                B.stats = stats; B.stat_index_global = sidx; B.acc4 = acc4; B.accw = accw; B.out_flow = out_flow;
-                const int pb = (B.strips_per_unit + PIPE2_THREADS / 32 - 1) / (PIPE2_THREADS / 32);
-                k_splat_pair<<<dim3(pb, nu), PIPE2_THREADS, 0, st>>>(B, u0);
-            } else {
-                k_splat_strip<MODE_F32><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
-            }
+            if (pair_ok) k_splat_pair<<<pgrid, PIPE2_THREADS, 0, st>>>(B, u0);
+            else k_splat_strip<MODE_F32><<<sgrid, TILE_THREADS, 0, st>>>(A, u0);
             prof_end(ctx, st);
-            LAUNCH_CHECK("k_splat_strip<f32>");
+            LAUNCH_CHECK("k_splat<f32>");
         }
         prof_begin(ctx, PK_NORMALISE, nu, st);
         if (rezero) {

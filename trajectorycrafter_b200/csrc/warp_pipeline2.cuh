@@ -134,3 +134,15 @@ k_normalise_pair(float4* __restrict__ acc4, float* __restrict__ accw, int unit0,
                        out_mask + (size_t)u * hw, out_depth ? out_depth + (size_t)u * hw : nullptr, bad);
     if (bad && range_flag) atomicOr(range_flag, 1);
 }
+
+// deterministic modes of the same strip code (per-chunk launches): MODE_WMAX = max emitted weight per cell,
+// MODE_I64 = order-free fixed-point sums relative to that maximum (see warp_strip.cuh emit<MODE_I64>)
+template <int MODE>
+__global__ void __launch_bounds__(PIPE2_THREADS, TCW_SPLAT_MINB)
+k_splat_pair_det(PairArgs A, int unit0) {
+    const int strip = blockIdx.x * (PIPE2_THREADS / 32) + (threadIdx.x >> 5);
+    if (strip >= A.strips_per_unit) return;
+    const int u = unit0 + blockIdx.y;
+    if (unit_is_pinhole(A.Mall + (size_t)u * M_FLOATS)) splat_pair_strip<true, PAIR_H_CHUNK, MODE>(A, u, blockIdx.y, strip);
+    else splat_pair_strip<false, PAIR_H_CHUNK, MODE>(A, u, blockIdx.y, strip);
+}
