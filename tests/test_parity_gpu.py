@@ -280,3 +280,35 @@ def test_graph_replay_follows_new_contents():
     assert torch.equal(replay[1], fresh[1]) and torch.equal(replay[3], fresh[3])
     assert torch.allclose(replay[0], fresh[0], atol=2e-6)
     assert not torch.equal(replay[3], first[3])
+
+
+@pytest.mark.parametrize("env", [{"TCW_PERSIST": "1"}, {"TCW_V3": "1"}, {"TCW_SERIAL": "1"}, {"TCW_SERIAL": "0"},
+                                 {"TCW_NO_GRAPH": "1"}, {"TCW_LANES": "2", "TCW_CHUNK_UNITS": "5"}, {"TCW_NO_PIPELINE": "1"}],
+                         ids=lambda e: "+".join(f"{k[4:]}={v}" for k, v in e.items()))
+def test_every_schedule_and_kernel_generation_vs_oracle(clip, env):
+    """The A/B switches select older kernels (TCW_V3), the persistent kernel (TCW_PERSIST) and other schedules of
+    the same kernels; all of them must meet the same parity bar (tcw_create reads the switches)."""
+    import os
+    frames, depths = clip
+    T1, T2, K, src = orbit_units(depths, 384, 672)
+    pick = torch.cat([torch.arange(8) + 8 * f for f in (3, 30)] + [torch.tensor([385, 391])])
+    M = prepare_matrices(T1[pick], T2[pick], K[pick])
+    os.environ.update(env)
+    try:
+        w2 = Warper(device="cuda:0")
+        w2._context()
+    finally:
+        for k in env:
+            os.environ.pop(k)
+    ref = oracle.forward_warp(frames, None, depths, M, src_index=src[pick].numpy(), per_unit_max=True)
+    n, dev = M.shape[0], w2.device
+    fd, dd, Md, sd = frames.to(dev), depths.to(dev), M.to(dev), src[pick].to(torch.int32).to(dev)
+    out = (torch.empty((n, 3, 384, 672), device=dev), torch.empty((n, 1, 384, 672), device=dev),
+           torch.empty((n, 1, 384, 672), device=dev), torch.empty((n, 2, 384, 672), device=dev))
+    flag = torch.zeros(1, dtype=torch.int32, device=dev)
+    for _ in range(3):       # three identical calls: plain enqueue, graph capture, graph replay (where enabled)
+        for t in out:
+            t.fill_(float("nan"))
+        got = w2.forward_warp_matrices(fd, dd, Md, src_index=sd, check_range=flag, out=out)
+        check_against(got, ref[0], ref[1], ref[2], ref[3])
+    assert int(flag.item()) == 0
