@@ -97,8 +97,7 @@ k_warp_pipeline2(Pipe2Args P) {
                 __nanosleep(500);
             }
         }
-        if (unit_is_pinhole(P.A.Mall + (size_t)u * M_FLOATS)) splat_pair_strip<true, PAIR_H>(P.A, u, u % P.ring, item);
-        else splat_pair_strip<false, PAIR_H>(P.A, u, u % P.ring, item);
+        splat_pair_strip<PAIR_H>(P.A, u, u % P.ring, item);
         __threadfence();
         __syncwarp();
         if (lane == 0) atomicAdd(&P.stats_rw[u].splat_done, 1);
@@ -117,8 +116,7 @@ k_splat_pair(PairArgs A, int unit0) {
     const int strip = blockIdx.x * (PIPE2_THREADS / 32) + (threadIdx.x >> 5);
     if (strip >= A.strips_per_unit) return;                          // whole warps leave together
     const int u = unit0 + blockIdx.y;
-    if (unit_is_pinhole(A.Mall + (size_t)u * M_FLOATS)) splat_pair_strip<true, PAIR_H_CHUNK>(A, u, blockIdx.y, strip);
-    else splat_pair_strip<false, PAIR_H_CHUNK>(A, u, blockIdx.y, strip);
+    splat_pair_strip<PAIR_H_CHUNK>(A, u, blockIdx.y, strip);
 }
 
 // normalise / mask / clip of a chunk of units as its own launch: each warp takes 128-pixel groups
@@ -143,6 +141,5 @@ k_splat_pair_det(PairArgs A, int unit0) {
     const int strip = blockIdx.x * (PIPE2_THREADS / 32) + (threadIdx.x >> 5);
     if (strip >= A.strips_per_unit) return;
     const int u = unit0 + blockIdx.y;
-    if (unit_is_pinhole(A.Mall + (size_t)u * M_FLOATS)) splat_pair_strip<true, PAIR_H_CHUNK, MODE>(A, u, blockIdx.y, strip);
-    else splat_pair_strip<false, PAIR_H_CHUNK, MODE>(A, u, blockIdx.y, strip);
+    splat_pair_strip<PAIR_H_CHUNK, MODE>(A, u, blockIdx.y, strip);
 }
