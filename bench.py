@@ -221,6 +221,12 @@ def run_ours(args):
     assert int(flag.item()) == 0, "range check failed"
     ms = max_over_ranks(ms_local)
     value = world * px_per_step / (ms * 1e-3) / 1e6
+    per_rank = None
+    if world > 1:      # which rank set the max, and at what clock (diagnosis of weak-scaling loss; not part of the metric)
+        mine = torch.tensor([ms_local, float(clocks.get("sm_mhz") or 0.0)], dtype=torch.float64, device=dev)
+        allr = [torch.zeros_like(mine) for _ in range(world)]
+        dist.all_gather(allr, mine)
+        per_rank = {"ms_per_step": [round(float(t[0]), 4) for t in allr], "sm_mhz": [float(t[1]) for t in allr]}
 
     # ---- roofline of the dominant kernel: CUDA-event durations of every launch, events recorded on the stream each
     # kernel is launched on.  Pass A repeats the timed schedule with per-launch events (four streams run
@@ -325,6 +331,28 @@ def run_ours(args):
         gather = {"ms": g_ms, "bytes_into_rank0": wire, "ingress_GBps": wire / (g_ms * 1e-3) / 1e9,
                   "what": "NCCL gather of colour f32 + mask u8 (13 B/px) of 49 units per rank to rank 0"}
 
+    # ---- next row of SURVEY.md §8f (N1), reported beside the metric, never part of it: the resize + pack kernel on
+    # the reference's own warp resolution, 49 x 576x1024 -> 384x672 (demo.py:91-100,117-120)
+    pack = None
+    if rank == 0 and world == 1:
+        Hs, Ws = 576, 1024
+        pf = torch.rand((N_FRAMES, 3, Hs, Ws), device=dev) * 2 - 1
+        pm = (torch.rand((N_FRAMES, 1, Hs, Ws), device=dev) > 0.2).float()
+        for _ in range(3):
+            warper.pack_condition(pf, pm, (H, W))
+        p0, p1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        p0.record()
+        for _ in range(10):
+            warper.pack_condition(pf, pm, (H, W))
+        p1.record()
+        torch.cuda.synchronize()
+        p_ms = p0.elapsed_time(p1) / 10
+        p_bytes = N_FRAMES * (Hs * Ws * 16 + H * W * 16)
+        pack = {"kernel": "k_resize_pack", "ms": p_ms, "shape": f"{N_FRAMES}x{Hs}x{Ws} -> {H}x{W}", "algorithmic_bytes": p_bytes,
+                "achieved_GBps": p_bytes / (p_ms * 1e-3) / 1e9, "frac_of_hbm_peak": p_bytes / (p_ms * 1e-3) / 1e9 / peak,
+                "note": "includes the two torch.empty output allocations of the Python entry; 462 MB in + 202 MB out, larger than L2"}
+        del pf, pm
+
     # ---- CPU baseline (rank 0, N=1 only): the oracle port on the host cores, one full step once
     cpu_baseline = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
@@ -346,6 +374,10 @@ def run_ours(args):
         }
         if gather is not None:
             line["gather"] = gather
+        if per_rank is not None:
+            line["per_rank"] = per_rank
+        if pack is not None:
+            line["pack_epilogue"] = pack
         print(json.dumps(line), flush=True)
     if world > 1:
         dist.barrier()

@@ -112,6 +112,16 @@ int tcw_splat(tcw_ctx* ctx, const float* frame, const float* mask1, const float*
 int tcw_clean_points(tcw_ctx* ctx, const float* frame, const float* mask2, int c, int h, int w,
                      double* out_frame, double* out_mask, void* cuda_stream);
 
+/*
+ * The step right after the warp loop, fused into one pass (reference demo.py:91-100, 117-120 -- inline code the
+ * reference repeats in every infer_* method, no function of its own):
+ *   out_video (3,n,h,w) = F.interpolate((frame + 1) / 2, (h,w), 'bilinear', align_corners=False).permute(1,0,2,3)
+ *   out_masks (1,n,h,w) = (1 - F.interpolate(mask, (h,w), 'nearest').permute(1,0,2,3)) * 255
+ *   frame (n,3,H,W) = warped colour in [-1,1], mask (n,1,H,W) = the warp's validity mask; all float32 device pointers.
+ */
+int tcw_resize_pack(tcw_ctx* ctx, const float* frame, const float* mask, int n, int H, int W, int h, int w,
+                    float* out_video, float* out_masks, void* cuda_stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -126,3 +126,15 @@ def contrib_count(flow):
     rc = lib().orc_contrib_count(_fp(flow), b, h, w, out.ctypes.data_as(ctypes.POINTER(ctypes.c_int)))
     assert rc == 0, rc
     return out
+
+
+def resize_pack(frame, mask, size):
+    """(cat(warped)+1)/2 -> bilinear resize -> (1,3,F,h,w);  (1 - nearest(mask)) * 255 -> (1,1,F,h,w)  (demo.py:91-100,117-120)."""
+    frame, mask = _f32(frame), _f32(mask)
+    n, _, H, W = frame.shape
+    h, w = int(size[0]), int(size[1])
+    video = np.empty((1, 3, n, h, w), np.float32)
+    masks = np.empty((1, 1, n, h, w), np.float32)
+    rc = lib().orc_resize_pack(_fp(frame), _fp(mask), n, H, W, h, w, _fp(video), _fp(masks))
+    assert rc == 0, rc
+    return video, masks

@@ -303,3 +303,63 @@ ORC_EXPORT int orc_contrib_count(const float* flow, int b, int h, int w, int* ou
     }
     return 0;
 }
+
+/*
+ * The step right after the warp loop (reference demo.py:91-100, 117-120):
+ *     cond_video = F.interpolate((cat(warped) + 1) / 2, size, mode='bilinear', align_corners=False)
+ *     cond_masks = F.interpolate(cat(masks), size, mode='nearest')
+ *     cond_video = cond_video.permute(1,0,2,3)[None]                  -> (1,3,F,h,w)
+ *     cond_masks = (1 - cond_masks.permute(1,0,2,3)[None]) * 255      -> (1,1,F,h,w)
+ * The arithmetic lives in torch (ATen UpSampleKernel.cpp, not vendored by the reference): restated
+ * from its published algorithm --
+ *   bilinear, align_corners=False, no scale_factor: scale = (float)in / out;
+ *     src = max(fma(scale, dst + 0.5f, -0.5f), 0);  i0 = min((int)src, in - 1);  l1 = clamp(src - i0, 0, 1);
+ *       (torch 2.11 CPU evaluates the source index with ONE rounding -- probed in this container: the two-rounding
+ *        form moves the weights by up to ulp(src) and misses the goldens by 1.6e-6, the fused form by 1.2e-7)
+ *     i1 = i0 + (i0 < in - 1);  l0 = 1 - l1;   (in == out: i0 = i1 = dst, l0 = 1, l1 = 0)
+ *     out = (a*lx0 + b*lx1) * ly0 + (c*lx0 + d*lx1) * ly1
+ *   nearest (legacy): src = min((int)floorf(dst * scale), in - 1)   (in == out: dst; out == 2 in: dst >> 1)
+ * ATen's vectorised kernel may contract products into FMAs, so parity of the colour is 1e-6 absolute
+ * (values in [0,1]); the packed mask is exact.  Pinned by tests/golden/pack_cases.npz (oracle/gen_golden_pack.py).
+ */
+static void lin_index(int dst, int in, int out, float scale, int* i0, int* i1, float* l0, float* l1) {
+    if (in == out) { *i0 = *i1 = dst; *l0 = 1.0f; *l1 = 0.0f; return; }
+    float src = fmaf(scale, (float)dst + 0.5f, -0.5f);   /* one rounding: what the ATen build pinned by the goldens does */
+    if (src < 0.0f) src = 0.0f;
+    int k = (int)floorf(src);
+    if (k > in - 1) k = in - 1;
+    float l = src - (float)k;
+    l = l < 0.0f ? 0.0f : (l > 1.0f ? 1.0f : l);
+    *i0 = k; *i1 = k + (k < in - 1 ? 1 : 0); *l1 = l; *l0 = 1.0f - l;
+}
+static int near_index(int dst, int in, int out, float scale) {
+    if (in == out) return dst;
+    if (out == 2 * in) return dst >> 1;
+    int k = (int)floorf((float)dst * scale);
+    return k < in - 1 ? k : in - 1;
+}
+ORC_EXPORT int orc_resize_pack(const float* frame, const float* mask, int n, int H, int W, int h, int w,
+                               float* out_video, float* out_masks) {
+    if (n < 0 || H <= 0 || W <= 0 || h <= 0 || w <= 0) return -1;
+    const size_t HW = (size_t)H * W, hw = (size_t)h * w;
+    const float sy = (float)H / (float)h, sx = (float)W / (float)w;
+    for (int f = 0; f < n; ++f) for (int y = 0; y < h; ++y) {
+        int y0, y1; float ly0, ly1;
+        lin_index(y, H, h, sy, &y0, &y1, &ly0, &ly1);
+        const int yn = near_index(y, H, h, sy);
+        for (int x = 0; x < w; ++x) {
+            int x0, x1; float lx0, lx1;
+            lin_index(x, W, w, sx, &x0, &x1, &lx0, &lx1);
+            for (int c = 0; c < 3; ++c) {
+                const float* s = frame + ((size_t)f * 3 + c) * HW;
+                const float a = (s[(size_t)y0 * W + x0] + 1.0f) / 2.0f, b = (s[(size_t)y0 * W + x1] + 1.0f) / 2.0f;
+                const float cc = (s[(size_t)y1 * W + x0] + 1.0f) / 2.0f, d = (s[(size_t)y1 * W + x1] + 1.0f) / 2.0f;
+                const float t0 = a * lx0 + b * lx1, t1 = cc * lx0 + d * lx1;
+                out_video[((size_t)c * n + f) * hw + (size_t)y * w + x] = t0 * ly0 + t1 * ly1;
+            }
+            const float m = mask[(size_t)f * HW + (size_t)yn * W + near_index(x, W, w, sx)];
+            out_masks[(size_t)f * hw + (size_t)y * w + x] = (1.0f - m) * 255.0f;
+        }
+    }
+    return 0;
+}

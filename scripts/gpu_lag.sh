@@ -1,4 +1,7 @@
-summ() { python -c "
-import sys,json
-d=json.loads(sys.stdin.read().strip().splitlines()[-1]); r=d['roofline']; print('$1 value',round(d['value']),'ms',round(d['ms_per_step'],3),'frac',round(r['frac'],3),'iso',{k:round(v,3) for k,v in r['per_kernel_ms_per_step'].items()})"; }
-for v in "" _contig; do TCW_LIB=$PWD/trajectorycrafter_b200/libtcwarp$v.so timeout 200 python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline 2>&1 | summ "lib$v"; done
+timeout 900 python -m pytest tests -x -q -m gpu 2>&1 | tail -4
+timeout 300 python bench.py --steps 20 --warmup 3 --no-e2e --no-cpu-baseline 2>&1 | tail -1 > gpurun_out/bench_pack.json; python - <<'PY'
+import json
+d=json.loads(open('gpurun_out/bench_pack.json').read().strip().splitlines()[-1])
+print('value',round(d['value']),'ms',round(d['ms_per_step'],3),'frac',round(d['roofline']['frac'],3),'step_frac',round(d['roofline']['step_frac'],3))
+print('pack',d.get('pack_epilogue'))
+PY

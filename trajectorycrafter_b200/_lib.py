@@ -33,6 +33,7 @@ SIGNATURES = {
     "tcw_splat": (c_int, [c_void_p, _FP, _FP, _FP, _FP, _FP, c_int, c_int, c_int, c_int, c_int,
                           _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
     "tcw_clean_points": (c_int, [c_void_p, _FP, _FP, c_int, c_int, c_int, _VP, _VP, c_void_p]),
+    "tcw_resize_pack": (c_int, [c_void_p, _FP, _FP, c_int, c_int, c_int, c_int, c_int, _FP, _FP, c_void_p]),
 }
 
 _lib = None

@@ -267,6 +267,7 @@ __device__ __forceinline__ float block_max_256(float v) {
 #include "warp_pipeline.cuh"
 #include "warp_pair.cuh"
 #include "warp_pipeline2.cuh"
+#include "resize_pack.cuh"
 
 // ----------------------------------------------------------------------------------------------
 // compute_transformed_points as a standalone op
@@ -895,6 +896,20 @@ TCW_API int tcw_clean_points(tcw_ctx* ctx, const float* frame, const float* mask
     const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
     k_clean_points<<<tiles_x * tiles_y, TILE_THREADS, 0, (cudaStream_t)cuda_stream>>>(frame, mask2, c, h, w, tiles_x, out_frame, out_mask);
     LAUNCH_CHECK("k_clean_points");
+    return TCW_OK;
+}
+
+TCW_API int tcw_resize_pack(tcw_ctx* ctx, const float* frame, const float* mask, int n, int H, int W, int h, int w,
+                            float* out_video, float* out_masks, void* cuda_stream) {
+    if (!ctx || !frame || !mask || !out_video || !out_masks) return fail(TCW_E_ARG, "tcw_resize_pack: NULL argument");
+    if (n <= 0 || H <= 0 || W <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_resize_pack: bad shape");
+    if ((size_t)h * w >= (1u << 31) || (size_t)H * W >= (1u << 31)) return fail(TCW_E_ARG, "tcw_resize_pack: image too large");
+    const size_t total = (size_t)n * h * w;
+    const size_t want = (total + 255) / 256;
+    const int blocks = (int)(want < (size_t)ctx->sm_count * 8 ? want : (size_t)ctx->sm_count * 8);
+    k_resize_pack<<<blocks, 256, 0, (cudaStream_t)cuda_stream>>>(frame, mask, n, H, W, h, w, (float)H / (float)h, (float)W / (float)w,
+                                                               out_video, out_masks);
+    LAUNCH_CHECK("k_resize_pack");
     return TCW_OK;
 }
 

@@ -333,6 +333,29 @@ class Warper:
         _lib.check(rc, "tcw_clean_points")
         return out, out_mask
 
+    def pack_condition(self, warped_frames, masks, sample_size):
+        """The lines every reference pipeline runs right after its warp loop (demo.py:91-100, 117-120), as one
+        kernel: ``cond_video = interpolate((warped + 1) / 2, sample_size, 'bilinear', align_corners=False)`` laid
+        out ``(1, 3, F, h, w)`` and ``cond_masks = (1 - interpolate(masks, sample_size, 'nearest')) * 255`` laid out
+        ``(1, 1, F, h, w)`` -- the two tensors the diffusion pipeline consumes.
+
+        warped_frames (F,3,H,W) float32 in [-1,1]; masks (F,1,H,W) float32 (``forward_warp_batch`` outputs).
+        The reference's ``mask=True`` variant hands float64 tensors to these lines; that is not covered here."""
+        assert warped_frames.dim() == 4 and warped_frames.shape[1] == 3, "warped_frames must be (F,3,H,W)"
+        n, _, H, W = warped_frames.shape
+        assert masks.shape == (n, 1, H, W), "masks must be (F,1,H,W)"
+        if warped_frames.dtype != torch.float32 or masks.dtype != torch.float32:
+            raise RuntimeError("pack_condition takes float32 tensors (the mask=False path of the reference)")
+        h, w = int(sample_size[0]), int(sample_size[1])
+        frame_d, mask_d = self._dev(warped_frames), self._dev(masks)
+        video = torch.empty((1, 3, n, h, w), dtype=torch.float32, device=self.device)
+        cmask = torch.empty((1, 1, n, h, w), dtype=torch.float32, device=self.device)
+        with torch.cuda.device(self.device):
+            rc = self._lib.tcw_resize_pack(self._context(), _ptr(frame_d), _ptr(mask_d), n, H, W, h, w,
+                                           _ptr(video), _ptr(cmask), self._stream())
+        _lib.check(rc, "tcw_resize_pack")
+        return video, cmask
+
     @staticmethod
     def create_grid(b, h, w):
         """models/utils.py:628-636: (b,2,h,w) int64 pixel grid, channel 0 = x, channel 1 = y."""
