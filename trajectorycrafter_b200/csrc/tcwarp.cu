@@ -813,11 +813,12 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
                                     out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
     }
-    const cudaError_t ie = cudaGraphInstantiate(&ctx->graph_exec, graph, 0);
+    cudaError_t ie = cudaGraphInstantiate(&ctx->graph_exec, graph, 0);
+    if (ie == cudaSuccess) ie = cudaGraphUpload(ctx->graph_exec, st);      // pre-pay the first-launch upload
     cudaGraphDestroy(graph);
     if (ie != cudaSuccess) {
         cudaGetLastError();
-        ctx->graph_exec = nullptr;
+        if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
         ctx->graphs_off = 1;
         return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
                                     out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);

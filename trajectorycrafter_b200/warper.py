@@ -36,6 +36,7 @@ class Warper:
         self._lib = _lib.load()            # raises if libtcwarp.so has not been built
         self._ctx = None
         self._workspace = None
+        self._checked_index = None
         return
 
     # ------------------------------------------------------------------ plumbing
@@ -137,7 +138,14 @@ class Warper:
             assert n == n_src, "src_index is required when the number of poses differs from the number of frames"
         else:
             assert src_index.shape == (n,)
-            assert int(src_index.min()) >= 0 and int(src_index.max()) < n_src
+            # range check on the host; a CUDA index tensor is checked once per (storage, version), not per call:
+            # reading it back would put a device sync into every submission
+            tag = (src_index.data_ptr(), src_index._version, n, n_src) if src_index.is_cuda else None
+            if tag is None or tag != self._checked_index:
+                assert int(src_index.min()) >= 0 and int(src_index.max()) < n_src
+                self._checked_index = tag
+        # tensors already resident on the device are used in place (no copy, no sync): a pageable host->device copy
+        # per call blocks the host until the previous submission has finished
         frames_d, depths_d, mask1_d = self._dev(frames), self._dev(depths), self._dev(mask1)
         M_d = M.to(self.device, torch.float32, non_blocking=True).contiguous()
         si_d = None if src_index is None else src_index.to(self.device, torch.int32).contiguous()
