@@ -1,4 +1,5 @@
-# tests + bench + ncu launch list + full captures of the dominant kernels; outputs under gpurun_out/<tag>
+# evidence round, part A: tests + bench lines + smoke + ncu launch list (one profiler pass per gpurun call);
+# part B (scripts/gpu_round_ncu.sh): ncu --set full captures.  Outputs under gpurun_out/<tag>
 TAG=${1:-r1}
 O=gpurun_out/$TAG
 mkdir -p $O
@@ -11,6 +12,4 @@ python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; tail -1 
 B="python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline"
 timeout 300 $B > $O/plain.log 2>&1 && \
 timeout 600 ncu --metrics gpu__time_duration.sum --clock-control none -s 800 -c 420 --csv --log-file $O/launches.csv $B > $O/ncu1.log 2>&1
-timeout 900 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"k_splat_pair|k_normalise_pair|k_zmax_quad" -s 60 -c 3 -o $O/kernels_full $B > $O/ncu2.log 2>&1
-TCW_SERIAL=1 TCW_CHUNK_UNITS=24 timeout 900 ncu --set full --clock-control none --cache-control none --import-source on -k regex:"k_splat_pair|k_normalise_pair" -s 12 -c 2 -o $O/kernels_full_24units $B > $O/ncu3.log 2>&1
 ls -la $O
