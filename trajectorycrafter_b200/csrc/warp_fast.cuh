@@ -41,6 +41,10 @@ k_zmax_quad(const float* __restrict__ depth, const int* __restrict__ src_index, 
     if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
     __syncthreads();
     const bool simple = M[27] == 0.0f && M[28] == 0.0f;
+    // pinhole K1^-1 (no skew, last row (0,0,1)): u = (m0 x + m2, m4 y + m5, 1) -- the zero products of the reference's
+    // dot products add +-0 to a non-zero partial sum, so dropping them changes no bit (same argument as warp_pair.cuh)
+    const bool pin = simple && M[1] == 0.0f && M[3] == 0.0f && M[6] == 0.0f && M[7] == 0.0f && M[8] == 1.0f;
+    const float m0 = M[0], m2 = M[2], m4 = M[4], m5 = M[5], t8 = M[17], t9 = M[18], t10 = M[19], t11 = M[20], k8 = M[29];
     const int s = src_index ? src_index[u] : u;
     const float* dsrc = depth + (size_t)s * h * w;
     const int wq = (w + 3) >> 2, quads = h * wq;
@@ -56,12 +60,27 @@ k_zmax_quad(const float* __restrict__ depth, const int* __restrict__ src_index, 
             #pragma unroll
             for (int i = 0; i < 4; ++i) d[i] = x0 + i < w ? dsrc[(size_t)y * w + x0 + i] : 0.0f;
         }
-        #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-            if (x0 + i < w) {
-                const float P2 = project_z(M, simple, (float)(x0 + i), (float)y, d[i]);
-                zs = fmaxf(zs, clampf(P2, 0.0f, 1000.0f));
-                za = fmaxf(za, fabsf(P2));
+        if (pin) {
+            const float u1 = __fadd_rn(__fmul_rn(m4, (float)y), m5);
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (x0 + i < w) {
+                    const float u0 = __fadd_rn(__fmul_rn(m0, (float)(x0 + i)), m2);
+                    const float X0 = __fmul_rn(d[i], u0), X1 = __fmul_rn(d[i], u1);
+                    const float Y2 = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(t8, X0), __fmul_rn(t9, X1)), __fmul_rn(t10, d[i])), t11);
+                    const float P2 = Y2 <= 0.01f ? 1000.0f : __fadd_rn(0.0f, __fmul_rn(k8, Y2));
+                    zs = fmaxf(zs, clampf(P2, 0.0f, 1000.0f));
+                    za = fmaxf(za, fabsf(P2));
+                }
+            }
+        } else {
+            #pragma unroll
+            for (int i = 0; i < 4; ++i) {
+                if (x0 + i < w) {
+                    const float P2 = project_z(M, simple, (float)(x0 + i), (float)y, d[i]);
+                    zs = fmaxf(zs, clampf(P2, 0.0f, 1000.0f));
+                    za = fmaxf(za, fabsf(P2));
+                }
             }
         }
     }
