@@ -29,7 +29,7 @@ ALGO_BYTES_PER_PX = 44.0          # read RGB 12 + depth 4, wri
 N_FRAMES, H, W = 49, 384, 672
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_splat_pair launch from the committed ncu --set full capture
 # (profiles/), for the 24-unit launch shape the roofline figure is quoted on
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 238_464_256   # profiles/r1_final_kernels_full_24units_ncu.txt: 109.05 MB read + 129.42 MB written
+NCU_TRAFFIC_BYTES_PER_LAUNCH = 238_216_960   # profiles/r1_final_kernels_full_24units_ncu.txt: 109.06 MB read + 129.16 MB written
 
 
 def load_peaks():
