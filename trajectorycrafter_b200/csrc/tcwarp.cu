@@ -18,6 +18,15 @@
 
 #define TCW_API extern "C" __attribute__((visibility("default")))
 
+#ifndef TCW_CONST_M
+#define TCW_CONST_M 0         // see warp_pair.cuh
+#endif
+#if TCW_CONST_M
+#include <atomic>
+struct tcw_ctx;
+static std::atomic<tcw_ctx*> g_const_owner{nullptr};      // the one context that may use the __constant__ matrix bank
+#endif
+
 // ----------------------------------------------------------------------------------------------
 // errors / context
 // ----------------------------------------------------------------------------------------------
@@ -165,6 +174,9 @@ TCW_API void tcw_destroy(tcw_ctx* c) {
     int prev = 0;
     cudaGetDevice(&prev);
     cudaSetDevice(c->device);
+#if TCW_CONST_M
+    { tcw_ctx* me = c; g_const_owner.compare_exchange_strong(me, nullptr); }
+#endif
     if (c->pool) cudaFree(c->pool);
     for (int i = 0; i < c->prof_cap; ++i) { cudaEventDestroy(c->prof[i].e0); cudaEventDestroy(c->prof[i].e1); }
     free(c->prof);
@@ -565,6 +577,16 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
                     k_zmax_quad<<<dim3(k0_bx, n_units - k0_head), TILE_THREADS, 0, st>>>(depth, src_index, M, k0_head, h, w, stats, n_units, 1);
                     LAUNCH_CHECK("k_zmax_quad");
                 }
+#if TCW_CONST_M
+                // one context per process may use the constant bank (a second one would overwrite it under running kernels)
+                bool use_cm = false;
+                if (n_units <= CONST_M_UNITS) {
+                    tcw_ctx* none = nullptr;
+                    use_cm = g_const_owner.compare_exchange_strong(none, ctx) || none == ctx;
+                }
+                if (use_cm) CUDA_TRY(cudaMemcpyToSymbolAsync(c_tcw_M, M, (size_t)n_units * M_FLOATS * sizeof(float), 0,
+                                                             cudaMemcpyDeviceToDevice, st));
+#endif
                 CUDA_TRY(cudaEventRecord(ctx->ev_splat[0], st));
                 for (int i = 0; i + 1 < NL; ++i) CUDA_TRY(cudaStreamWaitEvent(ctx->s_lane[i], ctx->ev_splat[0], 0));
                 if (k0_rest) {      // normalisers of the later rounds: own stream, concurrent with the first round of chunks
@@ -581,6 +603,10 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
                     B.acc4 = (float4*)buf;
                     B.accw = (float*)(buf + (size_t)g2 * hw * sizeof(float4));
                     prof_begin(ctx, PK_SPLAT, nu, sk);
+#if TCW_CONST_M
+                    if (use_cm) k_splat_pair_cm<<<dim3(pb, nu), PIPE2_THREADS, 0, sk>>>(B, u0);
+                    else
+#endif
                     k_splat_pair<<<dim3(pb, nu), PIPE2_THREADS, 0, sk>>>(B, u0);
                     prof_end(ctx, sk);
                     LAUNCH_CHECK("k_splat_pair");

@@ -119,6 +119,17 @@ k_splat_pair(PairArgs A, int unit0) {
     splat_pair_strip<PAIR_H_CHUNK>(A, u, blockIdx.y, strip);
 }
 
+#if TCW_CONST_M
+// same kernel reading the matrix blocks from __constant__ memory (tcw_forward_warp copies them there per call)
+__global__ void __launch_bounds__(PIPE2_THREADS, TCW_SPLAT_MINB)
+k_splat_pair_cm(PairArgs A, int unit0) {
+    const int strip = blockIdx.x * (PIPE2_THREADS / 32) + (threadIdx.x >> 5);
+    if (strip >= A.strips_per_unit) return;
+    const int u = unit0 + blockIdx.y;
+    splat_pair_strip<PAIR_H_CHUNK, MODE_F32, true>(A, u, blockIdx.y, strip);
+}
+#endif
+
 // normalise / mask / clip of a chunk of units as its own launch: each warp takes 128-pixel groups
 __global__ void __launch_bounds__(256)
 k_normalise_pair(float4* __restrict__ acc4, float* __restrict__ accw, int unit0, size_t hw,
