@@ -278,6 +278,12 @@ __device__ __forceinline__ float block_max_256(float v) {
 #include "warp_strip.cuh"
 #include "warp_pipeline.cuh"
 #include "warp_pair.cuh"
+#ifndef TCW_ROWS2
+#define TCW_ROWS2 0           // 1: next-round experiment, two source rows per iteration (warp_pair2.cuh); not in the default build
+#endif
+#if TCW_ROWS2
+#include "warp_pair2.cuh"
+#endif
 #include "warp_pipeline2.cuh"
 #include "resize_pack.cuh"
 

@@ -116,7 +116,11 @@ k_splat_pair(PairArgs A, int unit0) {
     const int strip = blockIdx.x * (PIPE2_THREADS / 32) + (threadIdx.x >> 5);
     if (strip >= A.strips_per_unit) return;                          // whole warps leave together
     const int u = unit0 + blockIdx.y;
+#if TCW_ROWS2
+    splat_pair_strip2<PAIR_H_CHUNK>(A, u, blockIdx.y, strip);
+#else
     splat_pair_strip<PAIR_H_CHUNK>(A, u, blockIdx.y, strip);
+#endif
 }
 
 #if TCW_CONST_M
