@@ -32,6 +32,10 @@ N_FRAMES, H, W = 49, 384, 672
 NCU_TRAFFIC_BYTES_PER_LAUNCH = 238_216_960   # profiles/r1_final_kernels_full_24units_ncu.txt: 109.06 MB read + 129.16 MB written
 
 
+ACCUMULATION = {"window": "fixed order: warp-private shared-memory windows + ordered gather (default, reproducible)",
+                "atomic": "fp32 L2 reductions (order varies run to run)", "integer": "int64 fixed point (order-free)"}
+
+
 def load_peaks():
     path = os.path.join(ROOT, "MEASURED_PEAKS.json")
     if os.path.exists(path):
@@ -204,7 +208,7 @@ def run_ours(args):
 
     def step():
         warper.forward_warp_matrices(frames_d, depths_d, M_d, src_index=src_d, per_frame_max=True,
-                                     check_range=flag, out=out, deterministic=args.deterministic)
+                                     check_range=flag, out=out, accumulation=args.accumulation)
 
     for _ in range(max(3, args.warmup)):
         step()
@@ -251,7 +255,7 @@ def run_ours(args):
 
         def one():
             w2.forward_warp_matrices(frames_d, depths_d, M_d, src_index=src_d, per_frame_max=True,
-                                     check_range=flag, out=out, deterministic=args.deterministic)
+                                     check_range=flag, out=out, accumulation=args.accumulation)
         for _ in range(2):
             one()
         torch.cuda.synchronize()
@@ -265,17 +269,17 @@ def run_ours(args):
         return res, n
 
     prof, prof_steps = profile_pass({})
-    iso, iso_steps = profile_pass({"TCW_SERIAL": "1", "TCW_CHUNK_UNITS": "24"})
+    iso, iso_steps = profile_pass({"TCW_LANES": "1", "TCW_CHUNK_UNITS": "24"})
     roofline = None
-    i_ms, i_n, i_units = iso["project_splat"]
-    k_ms, k_n, k_units = prof["project_splat"]
+    i_ms, i_n, i_units = iso["splat"]
+    k_ms, k_n, k_units = prof["splat"]
     if i_n and k_n:
         # headline: the kernel timed ALONE (pass B) -- a roofline fraction describes one kernel owning the GPU;
         # "overlapped" repeats the figure for the launches of the timed 4-lane schedule, which share the SMs with
         # the other lanes' kernels, and "step_frac" is the whole timed step against the same peak
         def ach(ms_, units_):
             return ALGO_BYTES_PER_PX * units_ * H * W / (ms_ * 1e-3) / 1e9
-        kname = "k_splat_pair_det<i64> (deterministic)" if args.deterministic else "k_splat_pair (fused project + splat)"
+        kname = {"window": "k_splat_window", "atomic": "k_splat_pair", "integer": "k_splat_pair_det<i64>"}[args.accumulation]
         tot_i, tot_k = sum(v[0] for v in iso.values()), sum(v[0] for v in prof.values())
         roofline = {"bound": "hbm", "kernel": kname, "achieved": ach(i_ms, i_units), "peak": peak, "unit": "GB/s",
                     "frac": ach(i_ms, i_units) / peak, "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH,
@@ -375,8 +379,7 @@ def run_ours(args):
             "metric": "warped_mpix_per_s", "value": value, "unit": "Mpix/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(workload_config(), accumulation="int64 fixed point (deterministic)" if args.deterministic
-                           else "fp32 L2 reductions", host_enqueue_ms_per_step=round(host_ms, 3)), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "config": dict(workload_config(), accumulation=ACCUMULATION[args.accumulation], host_enqueue_ms_per_step=round(host_ms, 3)), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "cpu_baseline": cpu_baseline,
         }
         if gather is not None:
@@ -397,7 +400,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--deterministic", action="store_true", help="order-independent int64 accumulation")
+    ap.add_argument("--accumulation", default="window", choices=sorted(ACCUMULATION))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()

@@ -24,14 +24,24 @@
 extern "C" {
 #endif
 
-#define TCW_VERSION 100
+#define TCW_VERSION 200
 
 /* flags */
 #define TCW_PER_UNIT_MAX   1   /* soft-z normaliser log_depth.max() taken per unit (== n_units reference calls with b=1);
                                   without it the max is over the whole call (== one reference call with b=n_units, models/utils.py:492) */
-#define TCW_DETERMINISTIC  2   /* order-independent integer accumulation: bitwise reproducible run to run */
+#define TCW_DETERMINISTIC  2   /* tcw_forward_warp: strict integer accumulation (per-cell maximum weight, then order-free int64 fixed-point sums).
+                                  Slow; the DEFAULT path (no mode flag) is already reproducible run to run: it sums every cell in a fixed order
+                                  (warp-private shared-memory windows, then an ordered gather) */
 #define TCW_CLEAN          4   /* fuse clean_points (models/utils.py:585-626): 5x5 dilation of the hole mask; out_frame/out_mask are then DOUBLE (float64) buffers */
 #define TCW_IS_IMAGE       8   /* tcw_splat only: holes = -1, range check, clamp to [-1,1] (models/utils.py:572-582) */
+#define TCW_ATOMIC_F32    16   /* tcw_forward_warp: opt-in float reductions into L2 accumulators (the round-1 kernel); the order of the
+                                  additions, and with it the last bits of colour / depth, varies from run to run */
+#define TCW_HOST_MASK_U8  32   /* tcw_forward_warp_host only: out_mask is a uint8 (n,1,h,w) host buffer (0 / 1), a quarter of the download */
+
+/* bits of *range_flag (status word) */
+#define TCW_STATUS_RANGE       1   /* a valid colour left [-1.1, 1.1] before the clamp: the reference's assert (models/utils.py:580-581) */
+#define TCW_STATUS_UNORDERED   2   /* a footprint did not fit the unit's slab pool and was reduced with float atomics (order not fixed) */
+#define TCW_STATUS_SRC_INDEX   4   /* src_index held a value outside [0, n_src); that unit read source 0 instead */
 
 /* error codes */
 #define TCW_OK              0
@@ -53,8 +63,8 @@ long long tcw_launch_count(const tcw_ctx* ctx);
 /*
  * Optional per-kernel device timing (CUDA events around every launch, on the launching stream).
  * tcw_profile_read synchronises on the recorded events, sums them per kernel class
- * [0]=depth-max pre-pass, [1]=project+splat, [2]=normalise, [3]=max-weight pre-pass of the
- * deterministic path, and resets the log.  ms/launches/units are arrays of 4; units = number of warp units those launches processed.
+ * [0]=pre-pass (default path: project + flow + boxes; opt-in modes: depth-max), [1]=splat, [2]=gather / normalise,
+ * [3]=max-weight pre-pass of the integer mode, and resets the log.  ms/launches/units are arrays of 4; units = number of warp units those launches processed.
  */
 int tcw_profile_enable(tcw_ctx* ctx, int enable);
 int tcw_profile_read(tcw_ctx* ctx, double* ms, long long* launches, double* units);
@@ -69,7 +79,8 @@ int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, int flags
  *   M (n_units,30) DEVICE pointer, layout above.
  *   out_frame (n_units,3,h,w)  out_mask (n_units,1,h,w)  out_depth (n_units,1,h,w) or NULL
  *   out_flow (n_units,2,h,w) or NULL
- *   range_flag: device int, OR-ed with 1 if a valid colour left [-1.1,1.1] (the reference's assert, :580-581); may be NULL.
+ *   range_flag: device int, OR-ed with TCW_STATUS_* bits (bit 0 = the reference's range assert, :580-581); may be NULL.
+ *   flags: TCW_PER_UNIT_MAX, TCW_CLEAN, and at most one mode flag (TCW_DETERMINISTIC | TCW_ATOMIC_F32).
  */
 int tcw_forward_warp(tcw_ctx* ctx,
                      const float* frame, const float* mask1, const float* depth,
@@ -97,7 +108,8 @@ int tcw_project(tcw_ctx* ctx, const float* depth, const int* src_index, const fl
 /*
  * Replaces Warper.bilinear_splatting (models/utils.py:422-583) for c in 1..4 channels.
  *   frame (b,c,h,w)  mask1 (b,1,h,w)|NULL  depth (b,h,w)  flow (b,2,h,w)  flow_mask (b,1,h,w)|NULL
- *   out (b,c,h,w)  out_mask (b,1,h,w).   flags: TCW_IS_IMAGE, TCW_PER_UNIT_MAX, TCW_DETERMINISTIC.
+ *   out (b,c,h,w)  out_mask (b,1,h,w).   flags: TCW_IS_IMAGE, TCW_PER_UNIT_MAX.  Runs the window kernels of the forward warp
+ *   (fixed summation order); the soft-z normaliser is taken over the whole call unless TCW_PER_UNIT_MAX is set (:490-492).
  */
 int tcw_splat(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
               const float* flow, const float* flow_mask, int b, int c, int h, int w, int flags,

@@ -30,7 +30,7 @@ def test_library_builds_and_exports_every_declared_symbol():
     for name in declared_symbols():
         assert hasattr(lib, name), f"{name} is declared in include/tcwarp.h but not exported"
     lib.tcw_version.restype = ctypes.c_int
-    assert lib.tcw_version() == 100
+    assert lib.tcw_version() == 200
 
 
 def test_python_binding_covers_the_header():

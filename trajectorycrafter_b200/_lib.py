@@ -13,6 +13,13 @@ TCW_PER_UNIT_MAX = 1
 TCW_DETERMINISTIC = 2
 TCW_CLEAN = 4
 TCW_IS_IMAGE = 8
+TCW_ATOMIC_F32 = 16
+TCW_HOST_MASK_U8 = 32
+# status bits a call ORs into its range_flag word
+TCW_STATUS_RANGE = 1
+TCW_STATUS_UNORDERED = 2
+TCW_STATUS_SRC_INDEX = 4
+VERSION = 200
 
 # every symbol include/tcwarp.h declares: name -> (restype, argtypes)
 _FP, _IP, _VP = c_void_p, c_void_p, c_void_p      # device/host pointers are passed as raw addresses
@@ -58,8 +65,8 @@ def load() -> ctypes.CDLL:
         fn = getattr(lib, name)          # AttributeError if the .so does not export a declared symbol
         fn.restype = res
         fn.argtypes = args
-    if lib.tcw_version() != 100:
-        raise TcwError(f"libtcwarp.so version {lib.tcw_version()} does not match the Python host (100)")
+    if lib.tcw_version() != VERSION:
+        raise TcwError(f"libtcwarp.so version {lib.tcw_version()} does not match the Python host ({VERSION}): rebuild it")
     _lib = lib
     return lib
 

@@ -35,7 +35,7 @@ __device__ float log1x_fwd(float a);      // warp_pair.cuh
 
 __global__ void __launch_bounds__(TILE_THREADS)
 k_zmax_quad(const float* __restrict__ depth, const int* __restrict__ src_index, const float* __restrict__ Mall,
-            int unit0, int h, int w, UnitStats* __restrict__ stats, int n_units_total, int poly_log) {
+            int unit0, int n_src, int h, int w, UnitStats* __restrict__ stats, int n_units_total, int poly_log) {
     __shared__ float M[M_FLOATS];
     const int u = unit0 + blockIdx.y;
     if (threadIdx.x < M_FLOATS) M[threadIdx.x] = Mall[(size_t)u * M_FLOATS + threadIdx.x];
@@ -45,7 +45,8 @@ k_zmax_quad(const float* __restrict__ depth, const int* __restrict__ src_index, 
     // dot products add +-0 to a non-zero partial sum, so dropping them changes no bit (same argument as warp_pair.cuh)
     const bool pin = simple && M[1] == 0.0f && M[3] == 0.0f && M[6] == 0.0f && M[7] == 0.0f && M[8] == 1.0f;
     const float m0 = M[0], m2 = M[2], m4 = M[4], m5 = M[5], t8 = M[17], t9 = M[18], t10 = M[19], t11 = M[20], k8 = M[29];
-    const int s = src_index ? src_index[u] : u;
+    int s = src_index ? src_index[u] : u;
+    if ((unsigned)s >= (unsigned)n_src) s = 0;      // reported by the splat kernel (TCW_STATUS_SRC_INDEX)
     const float* dsrc = depth + (size_t)s * h * w;
     const int wq = (w + 3) >> 2, quads = h * wq;
     const bool vec = (w & 3) == 0 && ((((size_t)dsrc) & 15) == 0);

@@ -1,0 +1,777 @@
+// warp_window.cuh — the DEFAULT forward-warp path: deterministic splat through warp-private shared-memory windows.
+// Included by tcwarp.cu after warp_pair.cuh (packed-fp32x2 helpers, log2x / exp2x, division helpers).
+//
+//   K1 k_win_prepass<PROJECT>  unproject / transform / project of every source pixel (models/utils.py:350-420):
+//                              writes flow12 (an output of the path anyway) and z', the per-unit soft-z normaliser,
+//                              and the EXACT target bounding box of every 32 x 8 source half-strip
+//   K2 k_splat_window          bilinear soft-z splat (models/utils.py:422-564) of one 64 x 8 source strip per warp into
+//                              a window of shared memory that only this warp touches: plain LDS / FADD / STS in
+//                              program order, no atomics; the window is then stored as one dense slab
+//   K3 k_gather_normalise      per 32 x 8 target tile: adds the slabs that overlap it in ascending half-strip
+//                              order, normalises, writes colour / mask / depth (models/utils.py:566-583)
+//
+// Determinism: every target cell is the sum of (a) contributions one warp added in its own program order and (b) the
+// slabs K3 adds in a fixed order, so the result does not depend on how warps are scheduled.  There is no float atomic on
+// this path when every half-strip's footprint fits the window (WIN_CAP cells); a larger footprint uses a slab in global
+// memory that still belongs to one warp only (vector reductions issued by that warp in program order); only a
+// footprint that does not fit the unit's slab pool at all is reduced into a shared plane (flagged in the status word).
+// Lanes that hit the same cell in ONE step are serialised through a tag array (see emit_window).
+#pragma once
+
+#ifndef TCW_WIN_CAP
+#define TCW_WIN_CAP 768            // cells of shared-memory window per warp (both half-strips together)
+#endif
+constexpr int WIN_CAP = TCW_WIN_CAP;
+constexpr int WIN_P4 = WIN_CAP + WIN_CAP / 8 + 1;            // float4 slots: one pad slot per 8 cells (stride-2 lanes stay conflict-free)
+constexpr int WIN_PW = WIN_CAP + WIN_CAP / 32 + 1;           // float slots: one pad word per 32 cells
+constexpr int WIN_BYTES = ((WIN_P4 * 16 + WIN_PW * 4 + WIN_CAP) + 15) / 16 * 16;
+constexpr int WIN_WARPS = 4;                                 // warps (strips) per CTA of K2
+constexpr int WIN_GROUP = 8;                                 // half-strips per K1 CTA = per box group
+constexpr int WIN_POOL_MULT = 3;                             // slab pool of a unit: WIN_POOL_MULT * h * w cells
+constexpr int WIN_MAXC = 256;                                // candidate half-strips one K3 CTA holds at a time
+
+struct WinBox { short x0, y0, bw, bh; int flags, pad; };     // cropped target coords; bw == 0: no cell.  flags bit 0: has pile pixels
+struct WinGrp { int x0, y0, x1, y1; };                       // union of WIN_GROUP boxes, [x0, x1) x [y0, y1); x1 <= x0: empty
+
+// What K1/K2/K3 share.  "prep slot" = where K1's per-unit data lives, "splat slot" = slab pool / spill plane of a unit in flight.
+struct WinArgs {
+    // sources
+    const float* frame; const float* mask1; const float* depth; const int* src_index; const float* Mall;
+    const float* gflow; const float* gflow_mask; int nv;     // generic splat (tcw_splat): flow given, nv value channels, depth = weight depth
+    int fused;                                               // 1: forward warp (values = RGB of frame[s] + z'), 0: generic splat
+    int n_src, h, w, strips_x, ns, nh, ng;
+    const UnitStats* stats; UnitStats* stats_rw; int stat_index_global; int n_units_total;
+    // K1 products
+    float* flow_out;                                         // (n,2,h,w) caller's flow12, or nullptr -> flowbuf
+    float* flowbuf; float* zbuf; WinBox* box; WinGrp* grp;   // per prep slot
+    // K2 products
+    int* counter; int* spill_flag; int* slab_off; float* pile;   // per splat slot
+    float4* pool4; float* poolw; long long pool_cells;
+    float4* spill4; float* spillw;
+    int* status;                                             // device word: bit 1 = a footprint was reduced into the shared plane, bit 2 = src_index out of range
+};
+
+__device__ __forceinline__ int win_src(const WinArgs& A, int u) {
+    int s = A.src_index ? A.src_index[u] : u;
+    if ((unsigned)s >= (unsigned)A.n_src) { if (A.status) atomicOr(A.status, 4); s = 0; }     // never read out of bounds
+    return s;
+}
+
+// ------------------------------------------------------------------------------------------------
+// K1: per source pixel flow12 = P.xy / P.z - grid and z' = P.z, bit-identical to the reference (scalar un-fused adds,
+// packed products, the correctly rounded packed division of warp_pair.cuh); per warp the target box of its half-strip.
+// One warp = 32 columns x 8 rows, lane = column, two rows (y, y + 1) per iteration as the packed pair.
+// PROJECT = false (generic splat): flow and depth are inputs; only the boxes and the normaliser are computed.
+// ------------------------------------------------------------------------------------------------
+template <bool PROJECT>
+__global__ void __launch_bounds__(WIN_GROUP * 32)
+k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
+    constexpr unsigned FULL = 0xffffffffu;
+    __shared__ int gb[4];
+    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    const int uc = blockIdx.y, u = unit0 + uc, ps = prep0 + uc;
+    const int h = A.h, w = A.w;
+    const size_t hw = (size_t)h * w;
+    if (threadIdx.x == 0) { gb[0] = INT_MAX; gb[1] = INT_MAX; gb[2] = INT_MIN; gb[3] = INT_MIN; }
+    if (blockIdx.x == 0 && threadIdx.x == 0 && slot0 >= 0) { A.counter[slot0 + uc] = 0; A.spill_flag[slot0 + uc] = 0; }
+    __syncthreads();
+    const int hs = blockIdx.x * WIN_GROUP + wv;
+    int xmin = INT_MAX, ymin = INT_MAX, xmax = INT_MIN, ymax = INT_MIN;
+    bool pile = false;
+    float zs = 0.0f;
+    if (hs < A.nh) {
+        const int hpr = 2 * A.strips_x;
+        const int sy = hs / hpr, hx = hs - sy * hpr;
+        const int x = hx * 32 + lane;
+        const bool ok = x < w;
+        const int xc = ok ? x : 0;
+        const int y0 = sy * 8, y1 = y0 + 8 < h ? y0 + 8 : h;
+        const int s = PROJECT ? win_src(A, u) : u;
+        const float fx = (float)x;
+        const float wf1 = (float)(w + 1), hf1 = (float)(h + 1);
+        const float* __restrict__ dp = A.depth + (size_t)s * hw;
+        float* __restrict__ flp = nullptr;
+        float* __restrict__ zp = nullptr;
+        const float* __restrict__ gfl = nullptr;
+        float m[9], T[12], K[9];
+        bool PIN = false;
+        float u0_pin = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f;
+        if (PROJECT) {
+            flp = A.flow_out ? A.flow_out + (size_t)u * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
+            zp = A.zbuf + (size_t)ps * hw;
+            const float* __restrict__ Mu = A.Mall + (size_t)u * M_FLOATS;
+            #pragma unroll
+            for (int i = 0; i < 9; ++i) m[i] = __ldg(Mu + i);
+            #pragma unroll
+            for (int i = 0; i < 12; ++i) T[i] = __ldg(Mu + 9 + i);
+            #pragma unroll
+            for (int i = 0; i < 9; ++i) K[i] = __ldg(Mu + 21 + i);
+            // pinhole zero pattern of K1^-1 and K2: the dropped terms are products with an exact 0 (see warp_pair.cuh)
+            PIN = m[1] == 0.0f && m[3] == 0.0f && m[6] == 0.0f && m[7] == 0.0f && m[8] == 1.0f &&
+                  K[1] == 0.0f && K[3] == 0.0f && K[6] == 0.0f && K[7] == 0.0f && K[8] == 1.0f;
+            a0 = __fmul_rn(m[0], fx); a1 = __fmul_rn(m[3], fx); a2 = __fmul_rn(m[6], fx);
+            u0_pin = __fadd_rn(a0, m[2]);
+        } else {
+            gfl = A.gflow + (size_t)u * 2 * hw;
+        }
+        for (int y = y0; y < y1; y += 2) {
+            const bool rowB = y + 1 < y1;
+            const float fyA = (float)y, fyB = (float)(y + 1);
+            const size_t qA = (size_t)y * w + xc, qB = rowB ? qA + w : qA;
+            float flxA, flxB, flyA, flyB, zA, zB;
+            if (PROJECT) {
+                const float dA = __ldg(dp + qA), dB = __ldg(dp + qB);
+                float P0A, P1A, P2A, P0B, P1B, P2B, Y2A, Y2B;
+                if (PIN) {
+                    const float u1A = __fadd_rn(__fmul_rn(m[4], fyA), m[5]), u1B = __fadd_rn(__fmul_rn(m[4], fyB), m[5]);
+                    const u64 d2 = pk(dA, dB);
+                    const u64 X0 = mul2(d2, pk1(u0_pin)), X1 = mul2(d2, pk(u1A, u1B));
+                    float a, b, c, e, f, g;
+                    upk(mul2(X0, pk1(T[0])), a, b); upk(mul2(X1, pk1(T[1])), c, e); upk(mul2(d2, pk1(T[2])), f, g);
+                    const float Y0A = __fadd_rn(__fadd_rn(__fadd_rn(a, c), f), T[3]), Y0B = __fadd_rn(__fadd_rn(__fadd_rn(b, e), g), T[3]);
+                    upk(mul2(X0, pk1(T[4])), a, b); upk(mul2(X1, pk1(T[5])), c, e); upk(mul2(d2, pk1(T[6])), f, g);
+                    const float Y1A = __fadd_rn(__fadd_rn(__fadd_rn(a, c), f), T[7]), Y1B = __fadd_rn(__fadd_rn(__fadd_rn(b, e), g), T[7]);
+                    upk(mul2(X0, pk1(T[8])), a, b); upk(mul2(X1, pk1(T[9])), c, e); upk(mul2(d2, pk1(T[10])), f, g);
+                    Y2A = __fadd_rn(__fadd_rn(__fadd_rn(a, c), f), T[11]); Y2B = __fadd_rn(__fadd_rn(__fadd_rn(b, e), g), T[11]);
+                    const u64 Y22 = pk(Y2A, Y2B);
+                    upk(mul2(pk(Y0A, Y0B), pk1(K[0])), a, b); upk(mul2(Y22, pk1(K[2])), c, e);
+                    P0A = __fadd_rn(a, c); P0B = __fadd_rn(b, e);
+                    upk(mul2(pk(Y1A, Y1B), pk1(K[4])), a, b); upk(mul2(Y22, pk1(K[5])), c, e);
+                    P1A = __fadd_rn(a, c); P1B = __fadd_rn(b, e);
+                    P2A = Y2A; P2B = Y2B;
+                } else {
+                    #pragma unroll
+                    for (int k = 0; k < 2; ++k) {
+                        const float d = k ? dB : dA, fy = k ? fyB : fyA;
+                        const float u0 = __fadd_rn(__fadd_rn(a0, __fmul_rn(m[1], fy)), m[2]);
+                        const float u1 = __fadd_rn(__fadd_rn(a1, __fmul_rn(m[4], fy)), m[5]);
+                        const float u2 = __fadd_rn(__fadd_rn(a2, __fmul_rn(m[7], fy)), m[8]);
+                        const float X0 = __fmul_rn(d, u0), X1 = __fmul_rn(d, u1), X2 = __fmul_rn(d, u2);
+                        const float Y0 = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[0], X0), __fmul_rn(T[1], X1)), __fmul_rn(T[2], X2)), T[3]);
+                        const float Y1 = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[4], X0), __fmul_rn(T[5], X1)), __fmul_rn(T[6], X2)), T[7]);
+                        const float Y2 = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[8], X0), __fmul_rn(T[9], X1)), __fmul_rn(T[10], X2)), T[11]);
+                        const float P0 = __fadd_rn(__fadd_rn(__fmul_rn(K[0], Y0), __fmul_rn(K[1], Y1)), __fmul_rn(K[2], Y2));
+                        const float P1 = __fadd_rn(__fadd_rn(__fmul_rn(K[3], Y0), __fmul_rn(K[4], Y1)), __fmul_rn(K[5], Y2));
+                        const float P2 = __fadd_rn(__fadd_rn(__fmul_rn(K[6], Y0), __fmul_rn(K[7], Y1)), __fmul_rn(K[8], Y2));
+                        if (k) { P0B = P0; P1B = P1; P2B = P2; Y2B = Y2; } else { P0A = P0; P1A = P1; P2A = P2; Y2A = Y2; }
+                    }
+                }
+                if (Y2A <= 0.01f) { P0A = 1000.0f; P1A = 1000.0f; P2A = 1000.0f; }      // behind the camera (:404-417)
+                if (Y2B <= 0.01f) { P0B = 1000.0f; P1B = 1000.0f; P2B = 1000.0f; }
+                u64 qx, qy;
+                {   // two IEEE divisions per pixel off one refined reciprocal (preconditions: warp_pair.cuh)
+                    const float zlo = fminf(P2A, P2B), zhi = fmaxf(P2A, P2B);
+                    const float nlo = fminf(fminf(fabsf(P0A), fabsf(P0B)), fminf(fabsf(P1A), fabsf(P1B)));
+                    const float nhi = fmaxf(fmaxf(fabsf(P0A), fabsf(P0B)), fmaxf(fabsf(P1A), fabsf(P1B)));
+                    const bool fast = zlo >= 9.5367431640625e-07f && zhi <= 1048576.0f && nlo >= 7.888609052210118e-31f && nhi <= 1.2676506002282294e30f;
+                    if (__all_sync(FULL, fast)) {
+                        const u64 b2 = pk(P2A, P2B), nb2 = pk(-P2A, -P2B);
+                        const u64 r = refine_rcp2(b2, nb2);
+                        qx = div2_with_rcp(pk(P0A, P0B), nb2, r);
+                        qy = div2_with_rcp(pk(P1A, P1B), nb2, r);
+                    } else {
+                        qx = pk(__fdiv_rn(P0A, P2A), __fdiv_rn(P0B, P2B));
+                        qy = pk(__fdiv_rn(P1A, P2A), __fdiv_rn(P1B, P2B));
+                    }
+                }
+                upk(sub2(qx, pk1(fx)), flxA, flxB);
+                upk(sub2(qy, pk(fyA, fyB)), flyA, flyB);
+                zA = P2A; zB = P2B;
+                if (ok) {
+                    __stcg(flp + qA, flxA); __stcg(flp + hw + qA, flyA); __stcg(zp + qA, zA);
+                    if (rowB) { __stcg(flp + qB, flxB); __stcg(flp + hw + qB, flyB); __stcg(zp + qB, zB); }
+                }
+            } else {
+                flxA = __ldg(gfl + qA); flyA = __ldg(gfl + hw + qA); zA = __ldg(dp + qA);
+                flxB = __ldg(gfl + qB); flyB = __ldg(gfl + hw + qB); zB = __ldg(dp + qB);
+            }
+            #pragma unroll
+            for (int k = 0; k < 2; ++k) {
+                if (!ok || (k && !rowB)) continue;
+                const float z = k ? zB : zA;
+                zs = fmaxf(zs, clampf(z, 0.0f, 1000.0f));
+                // same arithmetic as K2 (models/utils.py:450-452): off = (flow + grid) + 1
+                const float ox = __fadd_rn(__fadd_rn(k ? flxB : flxA, fx), 1.0f), oy = __fadd_rn(__fadd_rn(k ? flyB : flyA, k ? fyB : fyA), 1.0f);
+                if (ox == 2.0f && oy == 2.0f && w >= 2 && h >= 2) { pile = true; continue; }
+                if (!(ox > 0.0f && ox < wf1 && oy > 0.0f && oy < hf1)) continue;      // every corner in the pad ring
+                const float f0x = floorf(ox), f0y = floorf(oy);
+                const int ix0 = (int)f0x, iy0 = (int)f0y;
+                const int ix1 = ix0 + (ox != f0x ? 1 : 0), iy1 = iy0 + (oy != f0y ? 1 : 0);
+                const int xl = ix0 > 1 ? ix0 : 1, xh = ix1 < w ? ix1 : w, yl = iy0 > 1 ? iy0 : 1, yh = iy1 < h ? iy1 : h;
+                if (xl <= xh && yl <= yh) {
+                    xmin = min(xmin, xl - 1); xmax = max(xmax, xh - 1);
+                    ymin = min(ymin, yl - 1); ymax = max(ymax, yh - 1);
+                }
+            }
+        }
+    }
+    xmin = __reduce_min_sync(FULL, xmin); ymin = __reduce_min_sync(FULL, ymin);
+    xmax = __reduce_max_sync(FULL, xmax); ymax = __reduce_max_sync(FULL, ymax);
+    const bool anyp = __any_sync(FULL, pile);
+    const unsigned zbits = __reduce_max_sync(FULL, __float_as_uint(zs));          // zs >= 0: uint order == float order
+    if (lane == 0) {
+        if (hs < A.nh) {
+            WinBox b;
+            const bool some = xmax >= xmin;
+            b.x0 = some ? (short)xmin : 0; b.y0 = some ? (short)ymin : 0;
+            b.bw = some ? (short)(xmax - xmin + 1) : 0; b.bh = some ? (short)(ymax - ymin + 1) : 0;
+            b.flags = anyp ? 1 : 0; b.pad = 0;
+            A.box[(size_t)ps * A.nh + hs] = b;
+            if (some) { atomicMin(&gb[0], xmin); atomicMin(&gb[1], ymin); atomicMax(&gb[2], xmax + 1); atomicMax(&gb[3], ymax + 1); }
+        }
+        // log is monotone: one log per warp.  The polynomial K2 evaluates per pixel, so ld / L == 1 at the arg-max pixel
+        const float ld = log1x(__fadd_rn(1.0f, __uint_as_float(zbits)));
+        atomicMax(&A.stats_rw[u].lbits, __float_as_uint(ld));
+        atomicMax(&A.stats_rw[A.n_units_total].lbits, __float_as_uint(ld));
+    }
+    __syncthreads();
+    if (threadIdx.x == 0) {
+        WinGrp g; g.x0 = gb[0]; g.y0 = gb[1]; g.x1 = gb[2]; g.y1 = gb[3];
+        if (g.x1 == INT_MIN) { g.x0 = 0; g.y0 = 0; g.x1 = 0; g.y1 = 0; }
+        A.grp[(size_t)ps * A.ng + blockIdx.x] = g;
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K2: one warp = one 64 x 8 source strip, two horizontally adjacent pixels per lane (A = x0 + 2 lane, B = A + 1).
+// Lanes 0-15 cover the left half-strip, lanes 16-31 the right one; each half has its own window (its box from K1).
+// ------------------------------------------------------------------------------------------------
+enum { WM_SMEM = 0, WM_GLOBAL = 1 };
+
+struct WinOut {
+    // WM_SMEM
+    float4* s4; float* sw; unsigned char* tag;
+    // WM_GLOBAL: this warp's slab (or the unit's shared plane)
+    float4* g4; float* gw;
+};
+
+// One merged contribution.  Must be reached by all 32 lanes (id < 0: nothing to add).
+// WM_SMEM: read-modify-write of the warp's own window.  Two lanes with the same cell in this step are serialised:
+// every pending lane writes its number to the cell's tag, the lane that reads its own number back adds and leaves,
+// the others go round again.  Which of several same-address stores of one instruction survives is a fixed
+// function of that instruction (the hardware keeps the highest lane), so the order of the additions is fixed.
+template <int MODE>
+__device__ __forceinline__ void emit_window(const WinOut& o, int lane, int id, u64 rg, u64 bz, float sw) {
+    constexpr unsigned FULL = 0xffffffffu;
+    if (MODE == WM_GLOBAL) {
+        if (id >= 0) {
+            float r, g, b, z;
+            upk(rg, r, g); upk(bz, b, z);
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n\t"
+                         "red.global.add.f32 [%5], %6;"
+                         :: "l"(o.g4 + id), "f"(r), "f"(g), "f"(b), "f"(z), "l"(o.gw + id), "f"(sw) : "memory");
+        }
+        return;
+    }
+    bool pend = id >= 0;
+    if (!__any_sync(FULL, pend)) return;
+    const int p4 = id + (id >> 3), pw = id + (id >> 5);
+    do {
+        if (pend) o.tag[id] = (unsigned char)lane;
+        __syncwarp();
+        const bool win = pend && o.tag[id] == (unsigned char)lane;
+        if (win) {
+            float4 a = o.s4[p4];
+            float r, g, b, z;
+            upk(add2(pk(a.x, a.y), rg), r, g); upk(add2(pk(a.z, a.w), bz), b, z);
+            o.s4[p4] = make_float4(r, g, b, z);
+            o.sw[pw] += sw;
+        }
+        pend = pend && !win;
+        __syncwarp();
+    } while (__any_sync(FULL, pend));
+}
+template <int MODE>
+__device__ __forceinline__ void emit_window_single(const WinOut& o, int lane, bool take, int id, u64 rg, u64 bz, float w) {
+    const u64 w2 = pk1(w);
+    emit_window<MODE>(o, lane, take ? id : -1, mul2(rg, w2), mul2(bz, w2), w);
+}
+
+// per-unit source pointers of a strip
+struct WinSrc {
+    const float* fl;      // flow12 of the unit: x plane, y plane at + hw
+    const float* wd;      // weight depth plane (z' in the fused path, depth1 in the generic splat)
+    const float* v[4];    // value planes (nullptr: 0)
+    const float* m1; const float* fm;
+};
+
+// The eight rows of a strip in one mode.  `act` = this lane's half takes part in this pass; pitch / idbase = this lane's
+// window (padded floor coordinates -> cell index of the pass allocation: id = iy * pitch + ix + idbase).
+template <int MODE>
+__device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc& S, const WinOut& o, int lane, int x0s, int y0, int y1,
+                                                  bool act, int pitch, int idbase, float L, u64& hrg, u64& hbz, float& hwt, bool& any_pile) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int h = A.h, w = A.w;
+    const int xA = x0s + 2 * lane, xB = xA + 1;
+    const bool okA = xA < w && act, okB = xB < w && act;
+    const unsigned hw32 = (unsigned)((size_t)h * w);
+    const float fxA = (float)xA, fxB = (float)xB;
+    const u64 fx2 = pk(fxA, fxB);
+    float wf1 = (float)(w + 1), hf1 = (float)(h + 1);
+    const bool pile_ok = w >= 2 && h >= 2;
+    const int colA = xA < w ? xA : 0, colB = xB < w ? xB : 0;
+    const bool vec2 = xB < w && !(w & 1) &&
+        !((((size_t)S.fl) | ((size_t)S.wd) | ((size_t)S.v[0]) | ((size_t)S.v[1]) | ((size_t)S.v[2]) | ((size_t)S.v[3]) | ((size_t)S.m1) | ((size_t)S.fm)) & 7);
+    const bool vec2all = __all_sync(FULL, vec2 || !(xA < w));
+    // exact ld / L through a refined reciprocal (warp_pair.cuh)
+    const bool Lok = L >= 9.5367431640625e-07f;
+    float rL = rcp_approx(L);
+    rL = fmaf(rL, fmaf(-L, rL, 1.0f), rL);
+    const u64 rL2 = pk1(rL), nL2 = pk1(-L);
+
+    float flxA_n, flxB_n, flyA_n, flyB_n, zA_n, zB_n, vA_n[4], vB_n[4], mA_n = 1.f, mB_n = 1.f;
+    auto load_row = [&](int y) {
+        const unsigned q = (unsigned)y * (unsigned)w;
+        if (vec2all) {
+            const unsigned qa = q + colA;
+            const float2 f0 = __ldcg((const float2*)(S.fl + qa)), f1 = __ldcg((const float2*)(S.fl + hw32 + qa));
+            const float2 z2 = __ldcg((const float2*)(S.wd + qa));
+            flxA_n = f0.x; flxB_n = f0.y; flyA_n = f1.x; flyB_n = f1.y; zA_n = z2.x; zB_n = z2.y;
+            #pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (S.v[c]) { const float2 t = __ldg((const float2*)(S.v[c] + qa)); vA_n[c] = t.x; vB_n[c] = t.y; }
+                else { vA_n[c] = 0.f; vB_n[c] = 0.f; }
+            }
+            mA_n = 1.f; mB_n = 1.f;
+            if (S.m1) { const float2 t = __ldg((const float2*)(S.m1 + qa)); mA_n = t.x; mB_n = t.y; }
+            if (S.fm) { const float2 t = __ldg((const float2*)(S.fm + qa)); mA_n = __fmul_rn(mA_n, t.x); mB_n = __fmul_rn(mB_n, t.y); }
+        } else {
+            const unsigned qa = q + colA, qb = q + colB;
+            flxA_n = __ldcg(S.fl + qa); flxB_n = __ldcg(S.fl + qb); flyA_n = __ldcg(S.fl + hw32 + qa); flyB_n = __ldcg(S.fl + hw32 + qb);
+            zA_n = __ldcg(S.wd + qa); zB_n = __ldcg(S.wd + qb);
+            #pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (S.v[c]) { vA_n[c] = __ldg(S.v[c] + qa); vB_n[c] = __ldg(S.v[c] + qb); }
+                else { vA_n[c] = 0.f; vB_n[c] = 0.f; }
+            }
+            mA_n = 1.f; mB_n = 1.f;
+            if (S.m1) { mA_n = __ldg(S.m1 + qa); mB_n = __ldg(S.m1 + qb); }
+            if (S.fm) { mA_n = __fmul_rn(mA_n, __ldg(S.fm + qa)); mB_n = __fmul_rn(mB_n, __ldg(S.fm + qb)); }
+        }
+    };
+    load_row(y0);
+
+    for (int y = y0; y < y1; ++y) {
+        const float flxA = flxA_n, flxB = flxB_n, flyA = flyA_n, flyB = flyB_n, zA = zA_n, zB = zB_n;
+        float vA[4], vB[4];
+        #pragma unroll
+        for (int c = 0; c < 4; ++c) { vA[c] = vA_n[c]; vB[c] = vB_n[c]; }
+        const float mA = mA_n, mB = mB_n;
+        if (y + 1 < y1) load_row(y + 1);
+        const float fy = (float)y;
+
+        // ---- corner cells (models/utils.py:450-475), from the stored flow exactly as the reference forms them
+        const u64 ox2r = add2(add2(pk(flxA, flxB), fx2), pk1(1.0f)), oy2r = add2(add2(pk(flyA, flyB), pk1(fy)), pk1(1.0f));
+        float oxA, oxB, oyA, oyB;
+        upk(ox2r, oxA, oxB);
+        upk(oy2r, oyA, oyB);
+        const bool pileA = okA && pile_ok && oxA == 2.0f && oyA == 2.0f, pileB = okB && pile_ok && oxB == 2.0f && oyB == 2.0f;
+        bool liveA = okA && !pileA && oxA > 0.0f && oxA < wf1 && oyA > 0.0f && oyA < hf1;
+        bool liveB = okB && !pileB && oxB > 0.0f && oxB < wf1 && oyB > 0.0f && oyB < hf1;
+        // a pixel that adds nothing gets finite stand-in numbers: its products are exact zeros, never NaN
+        if (!liveA) { oxA = 1.5f; oyA = 1.5f; }
+        if (!liveB) { oxB = 1.5f; oyB = 1.5f; }
+        const u64 ox2 = pk(oxA, oxB), oy2 = pk(oyA, oyB);
+        const float fx0A = floorf(oxA), fx0B = floorf(oxB), fy0A = floorf(oyA), fy0B = floorf(oyB);
+        const int ix0A = (int)fx0A, ix0B = (int)fx0B, iy0A = (int)fy0A, iy0B = (int)fy0B;
+        const bool inA = (unsigned)(ix0A - 1) < (unsigned)(w - 1) && (unsigned)(iy0A - 1) < (unsigned)(h - 1);
+        const bool inB = (unsigned)(ix0B - 1) < (unsigned)(w - 1) && (unsigned)(iy0B - 1) < (unsigned)(h - 1);
+        const bool general = __any_sync(FULL, (liveA && !inA) || (liveB && !inB));
+
+        // ---- soft-z weight mg = mask1 * flow_mask * exp(-50 * log(1 + sat(z)) / L)   (:490-513)
+        u64 mg2;
+        {
+            const float sA = (liveA || pileA) ? clampf(zA, 0.0f, 1000.0f) : 0.0f, sB = (liveB || pileB) ? clampf(zB, 0.0f, 1000.0f) : 0.0f;
+            const u64 ld = log2x(add2(pk(sA, sB), pk1(1.0f)));
+            u64 qd;
+            if (Lok) qd = div2_with_rcp(ld, nL2, rL2);
+            else qd = pk(__fdiv_rn(plo(ld), L), __fdiv_rn(phi(ld), L));
+            mg2 = exp2x(mul2(qd, pk1(-50.0f)));
+            if (S.m1 || S.fm) mg2 = mul2(mg2, pk(mA, mB));
+        }
+        float mgA, mgB;
+        upk(mg2, mgA, mgB);
+        // values of the two pixels: (v0, v1), (v2, v3); the fused path splats z' itself as the fourth value
+        const float z3A = A.fused ? zA : vA[3], z3B = A.fused ? zB : vB[3];
+        u64 rgA = pk(vA[0], vA[1]), bzA = pk(vA[2], z3A), rgB = pk(vB[0], vB[1]), bzB = pk(vB[2], z3B);
+        if (pileA || pileB) {      // exactly on padded cell (2,2): four unit-proximity hits on output pixel (1,1) (behind-camera points)
+            any_pile = true;
+            const float pa = pileA ? mgA : 0.0f, pb = pileB ? mgB : 0.0f;
+            if (pileA) { hrg = fma2(rgA, pk1(pa), hrg); hbz = fma2(bzA, pk1(pa), hbz); }
+            if (pileB) { hrg = fma2(rgB, pk1(pb), hrg); hbz = fma2(bzB, pk1(pb), hbz); }
+            hwt += pa + pb;
+        }
+        if (!liveA) { mgA = 0.0f; rgA = 0; bzA = 0; }
+        if (!liveB) { mgB = 0.0f; rgB = 0; bzB = 0; }
+        mg2 = pk(mgA, mgB);
+
+        int idNWA, idSWA, idNEA, idSEA, idNWB, idSWB, idNEB, idSEB;
+        u64 wNW2, wSW2, wNE2, wSE2;
+        if (!general) {
+            const bool dxA = oxA != fx0A, dxB = oxB != fx0B, dyA = oyA != fy0A, dyB = oyB != fy0B;   // ceil == floor + 1 ?
+            const u64 fx02 = pk(fx0A, fx0B), fy02 = pk(fy0A, fy0B);
+            const u64 fx12 = pk(dxA ? fx0A + 1.0f : fx0A, dxB ? fx0B + 1.0f : fx0B);
+            const u64 fy12 = pk(dyA ? fy0A + 1.0f : fy0A, dyB ? fy0B + 1.0f : fy0B);
+            const u64 one2 = pk1(1.0f);
+            const u64 ax = sub2(one2, sub2(ox2, fx02)), bx = sub2(one2, sub2(fx12, ox2));
+            const u64 ay = sub2(one2, sub2(oy2, fy02)), by = sub2(one2, sub2(fy12, oy2));
+            wNW2 = mul2(mul2(ay, ax), mg2); wSW2 = mul2(mul2(by, ax), mg2);
+            wNE2 = mul2(mul2(ay, bx), mg2); wSE2 = mul2(mul2(by, bx), mg2);
+            // a pixel that adds nothing gets NEGATIVE ids: never emitted, can only "merge" with other negative ids
+            idNWA = liveA ? iy0A * pitch + ix0A + idbase : (int)0x80000000;
+            idNWB = liveB ? iy0B * pitch + ix0B + idbase : (int)0x80000000;
+            const int sA = liveA && dyA ? pitch : 0, sB = liveB && dyB ? pitch : 0;
+            const int eA = liveA && dxA ? 1 : 0, eB = liveB && dxB ? 1 : 0;
+            idSWA = idNWA + sA; idSWB = idNWB + sB;
+            idNEA = idNWA + eA; idNEB = idNWB + eB;
+            idSEA = idSWA + eA; idSEB = idSWB + eB;
+        } else {
+            // some live pixel touches the pad ring: the clamped formulas of the reference, corner by corner
+            const Corners ca = corners_from_flow(flxA, flyA, xA, y, h, w), cb = corners_from_flow(flxB, flyB, xB, y, h, w);
+            auto cid = [&](bool live, int ix, int iy) {
+                return (live && ix >= 1 && ix <= w && iy >= 1 && iy <= h) ? iy * pitch + ix + idbase : (int)0x80000000;
+            };
+            idNWA = cid(liveA, ca.ix0, ca.iy0); idSWA = cid(liveA, ca.ix0, ca.iy1); idNEA = cid(liveA, ca.ix1, ca.iy0); idSEA = cid(liveA, ca.ix1, ca.iy1);
+            idNWB = cid(liveB, cb.ix0, cb.iy0); idSWB = cid(liveB, cb.ix0, cb.iy1); idNEB = cid(liveB, cb.ix1, cb.iy0); idSEB = cid(liveB, cb.ix1, cb.iy1);
+            const float pa0 = liveA ? ca.nw : 0.f, pa1 = liveA ? ca.sw : 0.f, pa2 = liveA ? ca.ne : 0.f, pa3 = liveA ? ca.se : 0.f;
+            const float pb0 = liveB ? cb.nw : 0.f, pb1 = liveB ? cb.sw : 0.f, pb2 = liveB ? cb.ne : 0.f, pb3 = liveB ? cb.se : 0.f;
+            wNW2 = mul2(pk(pa0, pb0), mg2); wSW2 = mul2(pk(pa1, pb1), mg2);
+            wNE2 = mul2(pk(pa2, pb2), mg2); wSE2 = mul2(pk(pa3, pb3), mg2);
+        }
+        float wNWA, wNWB, wSWA, wSWB, wNEA, wNEB, wSEA, wSEB;
+        upk(wNW2, wNWA, wNWB); upk(wSW2, wSWA, wSWB); upk(wNE2, wNEA, wNEB); upk(wSE2, wSEA, wSEB);
+
+        // ---- register-level merge (the rules of warp_pair.cuh without the row carries: the window adds across rows).
+        // Destinations: Lt / Lb = pixel A's left cells, Mt / Mb = pixel B's left cells.  Sources: the left lane's B
+        // right-hand cells (rotate by one lane) and A's right-hand cells; what matches no destination is added on its own.
+        const int srcl = (lane + 31) & 31;
+        const int idNEl = __shfl_sync(FULL, idNEB, srcl), idSEl = __shfl_sync(FULL, idSEB, srcl);
+        const float wNEl = __shfl_sync(FULL, wNEB, srcl), wSEl = __shfl_sync(FULL, wSEB, srcl);
+        const u64 rgl = __shfl_sync(FULL, rgB, srcl), bzl = __shfl_sync(FULL, bzB, srcl);
+        u64 Ltrg = mul2(rgA, pk1(wNWA)), Ltbz = mul2(bzA, pk1(wNWA)), Lbrg = mul2(rgA, pk1(wSWA)), Lbbz = mul2(bzA, pk1(wSWA));
+        u64 Mtrg = mul2(rgB, pk1(wNWB)), Mtbz = mul2(bzB, pk1(wNWB)), Mbrg = mul2(rgB, pk1(wSWB)), Mbbz = mul2(bzB, pk1(wSWB));
+        u64 ANrg = mul2(rgA, pk1(wNEA)), ANbz = mul2(bzA, pk1(wNEA)), ASrg = mul2(rgA, pk1(wSEA)), ASbz = mul2(bzA, pk1(wSEA));
+        float Ltw = wNWA, Lbw = wSWA, Mtw = wNWB, Mbw = wSWB, ANw = wNEA, ASw = wSEA;
+        {   // the left lane's NE cell: my A's top-left, else my A's bottom-left, else my A's top-right
+            const bool a = idNEl == idNWA, b = !a && idNEl == idSWA, c = !a && !b && idNEl == idNEA;
+            const float wa = a ? wNEl : 0.0f, wb = b ? wNEl : 0.0f, wc = c ? wNEl : 0.0f;
+            Ltrg = fma2(rgl, pk1(wa), Ltrg); Ltbz = fma2(bzl, pk1(wa), Ltbz); Ltw += wa;
+            Lbrg = fma2(rgl, pk1(wb), Lbrg); Lbbz = fma2(bzl, pk1(wb), Lbbz); Lbw += wb;
+            ANrg = fma2(rgl, pk1(wc), ANrg); ANbz = fma2(bzl, pk1(wc), ANbz); ANw += wc;
+            emit_window_single<MODE>(o, lane, !(a || b || c), idNEl, rgl, bzl, wNEl);
+        }
+        {   // the left lane's SE cell: my A's bottom-left, else my A's top-left, else my A's bottom-right
+            const bool a = idSEl == idSWA, b = !a && idSEl == idNWA, c = !a && !b && idSEl == idSEA;
+            const float wa = a ? wSEl : 0.0f, wb = b ? wSEl : 0.0f, wc = c ? wSEl : 0.0f;
+            Lbrg = fma2(rgl, pk1(wa), Lbrg); Lbbz = fma2(bzl, pk1(wa), Lbbz); Lbw += wa;
+            Ltrg = fma2(rgl, pk1(wb), Ltrg); Ltbz = fma2(bzl, pk1(wb), Ltbz); Ltw += wb;
+            ASrg = fma2(rgl, pk1(wc), ASrg); ASbz = fma2(bzl, pk1(wc), ASbz); ASw += wc;
+            emit_window_single<MODE>(o, lane, !(a || b || c), idSEl, rgl, bzl, wSEl);
+        }
+        {   // A's NE sum: B's top-left, else B's bottom-left
+            const bool a = idNEA == idNWB, b = !a && idNEA == idSWB;
+            const float fa = a ? 1.0f : 0.0f, fb = b ? 1.0f : 0.0f;
+            Mtrg = fma2(ANrg, pk1(fa), Mtrg); Mtbz = fma2(ANbz, pk1(fa), Mtbz); Mtw = fmaf(ANw, fa, Mtw);
+            Mbrg = fma2(ANrg, pk1(fb), Mbrg); Mbbz = fma2(ANbz, pk1(fb), Mbbz); Mbw = fmaf(ANw, fb, Mbw);
+            emit_window<MODE>(o, lane, (a || b) ? -1 : idNEA, ANrg, ANbz, ANw);
+        }
+        {   // A's SE sum: B's bottom-left, else B's top-left
+            const bool a = idSEA == idSWB, b = !a && idSEA == idNWB;
+            const float fa = a ? 1.0f : 0.0f, fb = b ? 1.0f : 0.0f;
+            Mbrg = fma2(ASrg, pk1(fa), Mbrg); Mbbz = fma2(ASbz, pk1(fa), Mbbz); Mbw = fmaf(ASw, fa, Mbw);
+            Mtrg = fma2(ASrg, pk1(fb), Mtrg); Mtbz = fma2(ASbz, pk1(fb), Mtbz); Mtw = fmaf(ASw, fb, Mtw);
+            emit_window<MODE>(o, lane, (a || b) ? -1 : idSEA, ASrg, ASbz, ASw);
+        }
+        // pixels A and B in the same column: B's left cells are A's
+        const bool sT = idNWB == idNWA, sB = idSWB == idSWA;
+        {
+            const float fa = sT ? 1.0f : 0.0f, fb = sB ? 1.0f : 0.0f;
+            Ltrg = fma2(Mtrg, pk1(fa), Ltrg); Ltbz = fma2(Mtbz, pk1(fa), Ltbz); Ltw = fmaf(Mtw, fa, Ltw);
+            Lbrg = fma2(Mbrg, pk1(fb), Lbrg); Lbbz = fma2(Mbbz, pk1(fb), Lbbz); Lbw = fmaf(Mbw, fb, Lbw);
+        }
+        // (top and bottom cells of one pixel may coincide for an exact-integer y: they are added in separate steps)
+        emit_window<MODE>(o, lane, idNWA, Ltrg, Ltbz, Ltw);
+        emit_window<MODE>(o, lane, idSWA, Lbrg, Lbbz, Lbw);
+        emit_window<MODE>(o, lane, sT ? -1 : idNWB, Mtrg, Mtbz, Mtw);
+        emit_window<MODE>(o, lane, sB ? -1 : idSWB, Mbrg, Mbbz, Mbw);
+    }
+}
+
+__global__ void __launch_bounds__(WIN_WARPS * 32, 3)
+k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
+    constexpr unsigned FULL = 0xffffffffu;
+    extern __shared__ __align__(16) unsigned char win_smem[];
+    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    const int strip = blockIdx.x * WIN_WARPS + wv;
+    if (strip >= A.ns) return;                                           // whole warps leave together
+    const int uc = blockIdx.y, u = unit0 + uc, ps = prep0 + uc, sl = slot0 + uc;
+    const int h = A.h, w = A.w;
+    const size_t hw = (size_t)h * w;
+    const int sy = strip / A.strips_x, sx = strip - sy * A.strips_x;
+    const int hs0 = sy * 2 * A.strips_x + 2 * sx;
+    const int y0 = sy * 8, y1 = y0 + 8 < h ? y0 + 8 : h;
+
+    unsigned char* base = win_smem + (size_t)wv * WIN_BYTES;
+    WinOut o;
+    o.s4 = (float4*)base; o.sw = (float*)(base + WIN_P4 * 16); o.tag = base + WIN_P4 * 16 + WIN_PW * 4;
+    o.g4 = nullptr; o.gw = nullptr;
+
+    // sources of this unit
+    WinSrc S;
+    if (A.fused) {
+        const int s = win_src(A, u);
+        S.fl = A.flow_out ? A.flow_out + (size_t)u * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
+        S.wd = A.zbuf + (size_t)ps * hw;
+        S.v[0] = A.frame + (size_t)s * 3 * hw; S.v[1] = S.v[0] + hw; S.v[2] = S.v[1] + hw; S.v[3] = nullptr;
+        S.m1 = A.mask1 ? A.mask1 + (size_t)s * hw : nullptr; S.fm = nullptr;
+    } else {
+        S.fl = A.gflow + (size_t)u * 2 * hw;
+        S.wd = A.depth + (size_t)u * hw;
+        #pragma unroll
+        for (int c = 0; c < 4; ++c) S.v[c] = c < A.nv ? A.frame + ((size_t)u * A.nv + c) * hw : nullptr;
+        S.m1 = A.mask1 ? A.mask1 + (size_t)u * hw : nullptr;
+        S.fm = A.gflow_mask ? A.gflow_mask + (size_t)u * hw : nullptr;
+    }
+    const UnitStats* st = A.stats + (A.stat_index_global >= 0 ? A.stat_index_global : u);
+    const float L = __uint_as_float(st->lbits);
+
+    const WinBox b0 = A.box[(size_t)ps * A.nh + hs0], b1 = A.box[(size_t)ps * A.nh + hs0 + 1];
+    const int a0 = (int)b0.bw * b0.bh, a1 = (int)b1.bw * b1.bh;
+    int* offp = A.slab_off + (size_t)sl * A.nh + hs0;
+    float* pilep = A.pile + ((size_t)sl * A.ns + strip) * 8;
+    u64 hrg = 0, hbz = 0;
+    float hwt = 0.f;
+    bool any_pile = false;
+    int off0 = -1, off1 = -1;
+
+    if (a0 + a1 > 0 || ((b0.flags | b1.flags) & 1)) {
+        const int half = lane >> 4;
+        // passes: both halves in one window if they fit together, else one half per pass
+        const bool together = a0 + a1 <= WIN_CAP;
+        const int npass = together ? 1 : 2;
+        for (int p = 0; p < npass; ++p) {
+            const bool act0 = together || p == 0, act1 = together || p == 1;
+            const int n0 = act0 ? a0 : 0, n1 = act1 ? a1 : 0, cells = n0 + n1;
+            const bool pile_only = cells == 0;
+            if (pile_only && !(((act0 ? b0.flags : 0) | (act1 ? b1.flags : 0)) & 1)) continue;
+            // window of this lane's half for this pass
+            const bool act = half ? act1 : act0;
+            const WinBox& bm = half ? b1 : b0;
+            const int pitch = bm.bw;
+            int mode = cells <= WIN_CAP ? WM_SMEM : WM_GLOBAL;
+            long long off = 0;
+            bool shared_plane = false;
+            if (cells > 0) {
+                if (lane == 0) off = (long long)atomicAdd(A.counter + sl, cells);
+                off = __shfl_sync(FULL, off, 0);
+                if (off + cells > A.pool_cells || off < 0) { shared_plane = true; mode = WM_GLOBAL; }      // pool exhausted (the counter may wrap for absurd inputs)
+            }
+            int idbase;
+            if (shared_plane) {
+                // the unit's shared accumulation plane: global cell ids, float reductions (order not fixed) -- flagged
+                o.g4 = A.spill4 + (size_t)sl * hw; o.gw = A.spillw + (size_t)sl * hw;
+                idbase = -(w + 1);
+                if (lane == 0) { A.spill_flag[sl] = 1; if (A.status) atomicOr(A.status, 2); }
+            } else {
+                idbase = (half && act0 ? n0 : 0) - ((int)bm.y0 + 1) * pitch - ((int)bm.x0 + 1);
+                o.g4 = A.pool4 + (size_t)sl * A.pool_cells + off; o.gw = A.poolw + (size_t)sl * A.pool_cells + off;
+            }
+            const int pitch_l = shared_plane ? w : pitch;
+            if (mode == WM_SMEM) {
+                const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                const int n4 = cells + (cells >> 3) + 1, nw = cells + (cells >> 5) + 1;
+                for (int i = lane; i < n4; i += 32) o.s4[i] = z4;
+                for (int i = lane; i < nw; i += 32) o.sw[i] = 0.f;
+                __syncwarp();
+                splat_window_rows<WM_SMEM>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
+                __syncwarp();
+                // the window becomes a dense slab (cells in window order == slab order)
+                for (int i = lane; i < cells; i += 32) {
+                    __stcg(o.g4 + i, o.s4[i + (i >> 3)]);
+                    __stcg(o.gw + i, o.sw[i + (i >> 5)]);
+                }
+                __syncwarp();
+            } else {
+                if (!shared_plane) {
+                    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    for (int i = lane; i < cells; i += 32) { o.g4[i] = z4; o.gw[i] = 0.f; }
+                    __threadfence();      // the zeros are in L2 before this warp's first reduction arrives
+                    __syncwarp();
+                }
+                splat_window_rows<WM_GLOBAL>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
+            }
+            if (!shared_plane) {
+                if (act0 && a0 > 0) off0 = (int)off;
+                if (act1 && a1 > 0) off1 = (int)off + n0;
+            }
+        }
+    }
+    if (lane == 0) { offp[0] = off0; offp[1] = off1; }
+    // pixels that sat exactly on padded cell (2,2): one sum per strip, added by K3 to output pixel (1,1)
+    float hr = 0.f, hg = 0.f, hb = 0.f, hz = 0.f;
+    const bool anyp = __any_sync(FULL, any_pile);
+    if (anyp) {
+        upk(hrg, hr, hg);
+        upk(hbz, hb, hz);
+        #pragma unroll
+        for (int ofs = 16; ofs > 0; ofs >>= 1) {
+            hr += __shfl_xor_sync(FULL, hr, ofs); hg += __shfl_xor_sync(FULL, hg, ofs); hb += __shfl_xor_sync(FULL, hb, ofs);
+            hz += __shfl_xor_sync(FULL, hz, ofs); hwt += __shfl_xor_sync(FULL, hwt, ofs);
+        }
+    }
+    if (lane == 0) {
+        *(float4*)pilep = make_float4(4.f * hr, 4.f * hg, 4.f * hb, 4.f * hz);
+        *(float4*)(pilep + 4) = make_float4(4.f * hwt, anyp ? 1.f : 0.f, 0.f, 0.f);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// K3: CTA = 32 x 32 target tile, warp = 32 columns x 8 rows (lane = column, 8 rows of sums in registers).
+// Warp 0 lists the half-strips whose box overlaps the tile in ascending order (box groups first); every warp then
+// adds the listed slabs in that order, the shared plane if the unit used it, the pile sums (output pixel (1,1) only),
+// normalises and stores.  `is_image`: holes = -1, range check, clamp (models/utils.py:571-582).
+// ------------------------------------------------------------------------------------------------
+struct WinNormArgs {
+    float* out_frame; int out_c;          // (n, out_c, h, w): channels 0 .. out_c-1 of the sums / sum w
+    float* out_mask; float* out_depth;    // out_depth: fourth sum / sum w (fused path), may be nullptr
+    int is_image; int* range_flag;
+};
+
+__global__ void __launch_bounds__(128)
+k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, int tiles_x) {
+    constexpr unsigned FULL = 0xffffffffu;
+    __shared__ int cand[WIN_MAXC];
+    __shared__ int ncand, scan_pos;
+    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    const int uc = blockIdx.y, u = unit0 + uc, ps = prep0 + uc, sl = slot0 + uc;
+    const int h = A.h, w = A.w;
+    const size_t hw = (size_t)h * w;
+    const int ty_t = blockIdx.x / tiles_x, tx_t = blockIdx.x - ty_t * tiles_x;
+    const int X0 = tx_t * 32, Y0 = ty_t * 32, X1 = X0 + 32 < w ? X0 + 32 : w, Y1 = Y0 + 32 < h ? Y0 + 32 : h;
+    const int tx = X0 + lane, row0 = Y0 + wv * 8;
+    const WinBox* __restrict__ box = A.box + (size_t)ps * A.nh;
+    const WinGrp* __restrict__ grp = A.grp + (size_t)ps * A.ng;
+    const int* __restrict__ soff = A.slab_off + (size_t)sl * A.nh;
+    const float4* __restrict__ p4 = A.pool4 + (size_t)sl * A.pool_cells;
+    const float* __restrict__ pw = A.poolw + (size_t)sl * A.pool_cells;
+
+    float4 acc[8];
+    float accw[8];
+    #pragma unroll
+    for (int r = 0; r < 8; ++r) { acc[r] = make_float4(0.f, 0.f, 0.f, 0.f); accw[r] = 0.f; }
+
+    if (threadIdx.x == 0) scan_pos = 0;
+    __syncthreads();
+    while (true) {
+        // ---- warp 0: next batch of overlapping half-strips, ascending
+        if (wv == 0) {
+            int n = 0, g = scan_pos;              // scan_pos counts half-strips already examined (multiple of WIN_GROUP except at the end)
+            while (g < A.nh && n + 32 * WIN_GROUP <= WIN_MAXC) {
+                // 32 groups per step
+                const int gi = g / WIN_GROUP + lane;
+                bool hit = false;
+                if (gi < A.ng) { const WinGrp q = grp[gi]; hit = q.x0 < X1 && q.x1 > X0 && q.y0 < Y1 && q.y1 > Y0; }
+                unsigned hits = __ballot_sync(FULL, hit);
+                while (hits) {
+                    const int k = __ffs(hits) - 1;
+                    hits &= hits - 1;
+                    const int hsb = (g / WIN_GROUP + k) * WIN_GROUP;
+                    bool in = false;
+                    if (lane < WIN_GROUP && hsb + lane < A.nh) {
+                        const WinBox b = box[hsb + lane];
+                        in = b.bw > 0 && b.x0 < X1 && b.x0 + b.bw > X0 && b.y0 < Y1 && b.y0 + b.bh > Y0 && soff[hsb + lane] >= 0;
+                    }
+                    const unsigned m = __ballot_sync(FULL, in);
+                    if (in) cand[n + __popc(m & ((1u << lane) - 1))] = hsb + lane;
+                    n += __popc(m);
+                }
+                g += 32 * WIN_GROUP;
+            }
+            if (lane == 0) { ncand = n; scan_pos = g; }
+        }
+        __syncthreads();
+        const int n = ncand;
+        const bool more = scan_pos < A.nh;
+        // ---- every warp: add the listed slabs to its 32 x 8 cells
+        for (int i = 0; i < n; ++i) {
+            const int hs = cand[i];
+            const WinBox b = box[hs];
+            const int off = soff[hs];
+            const int ry0 = b.y0 > row0 ? b.y0 : row0, ry1 = (b.y0 + b.bh) < (row0 + 8) ? (b.y0 + b.bh) : (row0 + 8);
+            if (ry0 >= ry1) continue;                                     // warp-uniform
+            const bool colin = tx >= b.x0 && tx < b.x0 + b.bw;
+            const int cbase = off + (row0 - b.y0) * b.bw + (tx - b.x0);
+            #pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                if (row0 + r >= ry0 && row0 + r < ry1 && colin) {
+                    const int ci = cbase + r * b.bw;
+                    const float4 s = __ldcg(p4 + ci);
+                    const float sw = __ldcg(pw + ci);
+                    acc[r].x += s.x; acc[r].y += s.y; acc[r].z += s.z; acc[r].w += s.w; accw[r] += sw;
+                }
+            }
+        }
+        __syncthreads();
+        if (!more) break;
+    }
+    // ---- the unit's shared plane (only when a footprint did not fit the slab pool); re-zeroed for the next unit
+    if (A.spill_flag[sl]) {
+        float4* s4 = A.spill4 + (size_t)sl * hw;
+        float* sw = A.spillw + (size_t)sl * hw;
+        #pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            if (row0 + r < h && tx < w) {
+                const size_t p = (size_t)(row0 + r) * w + tx;
+                const float4 s = __ldcg(s4 + p);
+                const float t = __ldcg(sw + p);
+                acc[r].x += s.x; acc[r].y += s.y; acc[r].z += s.z; acc[r].w += s.w; accw[r] += t;
+                s4[p] = make_float4(0.f, 0.f, 0.f, 0.f); sw[p] = 0.f;
+            }
+        }
+    }
+    // ---- pile sums -> output pixel (1,1): strips in ascending order
+    if (blockIdx.x == 0 && wv == 0 && w >= 2 && h >= 2) {
+        const float* __restrict__ pile = A.pile + (size_t)sl * A.ns * 8;
+        float4 t4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        float tw = 0.f;
+        for (int s0 = 0; s0 < A.ns; s0 += 32) {
+            float4 a = make_float4(0.f, 0.f, 0.f, 0.f), bq = a;
+            if (s0 + lane < A.ns) { a = __ldcg((const float4*)(pile + (size_t)(s0 + lane) * 8)); bq = __ldcg((const float4*)(pile + (size_t)(s0 + lane) * 8 + 4)); }
+            unsigned m = __ballot_sync(FULL, bq.y != 0.f);
+            while (m) {
+                const int k = __ffs(m) - 1;
+                m &= m - 1;
+                t4.x += __shfl_sync(FULL, a.x, k); t4.y += __shfl_sync(FULL, a.y, k); t4.z += __shfl_sync(FULL, a.z, k);
+                t4.w += __shfl_sync(FULL, a.w, k); tw += __shfl_sync(FULL, bq.x, k);
+            }
+        }
+        if (lane == 1) { acc[1].x += t4.x; acc[1].y += t4.y; acc[1].z += t4.z; acc[1].w += t4.w; accw[1] += tw; }
+    }
+    // ---- normalise, mask, clip (models/utils.py:571-583)
+    bool bad = false;
+    if (tx < w) {
+        #pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int ty = row0 + r;
+            if (ty >= h) break;
+            const size_t p = (size_t)ty * w + tx;
+            const float W = accw[r];
+            const bool valid = W > 0.0f;
+            float rr = rcp_approx(W);
+            rr = fmaf(rr, fmaf(-W, rr, 1.0f), rr);
+            float v[4] = {acc[r].x * rr, acc[r].y * rr, acc[r].z * rr, acc[r].w * rr};
+            const float hole = N.is_image ? -1.0f : 0.0f;
+            #pragma unroll
+            for (int c = 0; c < 4; ++c) {
+                if (c < N.out_c) {
+                    float x = valid ? v[c] : hole;
+                    if (N.is_image) { bad |= !(fabsf(x) <= 1.1f); x = clampf(x, -1.0f, 1.0f); }
+                    __stcs(N.out_frame + ((size_t)u * N.out_c + c) * hw + p, x);
+                }
+            }
+            __stcs(N.out_mask + (size_t)u * hw + p, valid ? 1.0f : 0.0f);
+            if (N.out_depth) __stcs(N.out_depth + (size_t)u * hw + p, valid ? v[3] : 0.0f);
+        }
+    }
+    if (bad && N.range_flag) atomicOr(N.range_flag, 1);
+}

@@ -36,7 +36,6 @@ class Warper:
         self._lib = _lib.load()            # raises if libtcwarp.so has not been built
         self._ctx = None
         self._workspace = None
-        self._checked_index = None
         return
 
     # ------------------------------------------------------------------ plumbing
@@ -88,7 +87,7 @@ class Warper:
         n = (ctypes.c_longlong * 4)()
         units = (ctypes.c_double * 4)()
         _lib.check(self._lib.tcw_profile_read(self._context(), ms, n, units), "tcw_profile_read")
-        names = ("zmax", "project_splat", "normalise", "wmax")
+        names = ("prepass", "splat", "normalise", "wmax")
         return {k: (ms[i], int(n[i]), units[i]) for i, k in enumerate(names)}
 
     # ------------------------------------------------------------------ batched fast entry
@@ -98,7 +97,7 @@ class Warper:
                            mask1: Optional[torch.Tensor] = None, src_index: Optional[torch.Tensor] = None,
                            per_frame_max: bool = True, mask: bool = False,
                            return_depth: bool = True, return_flow: bool = True, check_range: bool = True,
-                           deterministic: bool = False):
+                           accumulation: str = "window"):
         """All (source frame, pose) units of a clip in ONE submission.
 
         Equivalent to looping the reference's ``forward_warp(frames[s:s+1], mask1[s:s+1],
@@ -109,6 +108,9 @@ class Warper:
         frames (n_src,3,h,w), depths (n_src,1,h,w), matrices (n_units,...).
         Returns (warped (n,3,h,w), mask (n,1,h,w), depth (n,1,h,w)|None, flow12 (n,2,h,w)|None);
         warped/mask are float64 when ``mask=True`` (reference quirk, models/utils.py:618-626).
+        ``accumulation``: "window" (default: every target cell is summed in a fixed order, results are bitwise
+        reproducible), "integer" (strict order-free int64 sums, slow) or "atomic" (float reductions in L2,
+        last bits vary from run to run).
         """
         n = transformation1.shape[0]
         M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
@@ -116,13 +118,13 @@ class Warper:
         return self.forward_warp_matrices(frames, depths, M, mask1=mask1, src_index=src_index,
                                           per_frame_max=per_frame_max, mask=mask, return_depth=return_depth,
                                           return_flow=return_flow, check_range=check_range,
-                                          deterministic=deterministic)
+                                          accumulation=accumulation)
 
     def forward_warp_matrices(self, frames: torch.Tensor, depths: torch.Tensor, M: torch.Tensor,
                               mask1: Optional[torch.Tensor] = None, src_index: Optional[torch.Tensor] = None,
                               per_frame_max: bool = True, mask: bool = False,
                               return_depth: bool = True, return_flow: bool = True, check_range=True,
-                              deterministic: bool = False, out=None):
+                              accumulation: str = "window", out=None):
         """``forward_warp_batch`` on an already prepared (n_units,30) matrix block
         (``prepare_matrices``): [K1^-1 | rows 0..2 of T2*T1^-1 | K2] per unit.
 
@@ -138,19 +140,17 @@ class Warper:
             assert n == n_src, "src_index is required when the number of poses differs from the number of frames"
         else:
             assert src_index.shape == (n,)
-            # range check on the host; a CUDA index tensor is checked once per (storage, version), not per call:
-            # reading it back would put a device sync into every submission
-            tag = (src_index.data_ptr(), src_index._version, n, n_src) if src_index.is_cuda else None
-            if tag is None or tag != self._checked_index:
-                assert int(src_index.min()) >= 0 and int(src_index.max()) < n_src
-                self._checked_index = tag
+            # a host index vector is checked here; a CUDA one is checked by the kernels that read it (an out-of-range
+            # entry reads source 0 and sets TCW_STATUS_SRC_INDEX in the status word) -- no device sync per submission
+            if not src_index.is_cuda:
+                assert int(src_index.min()) >= 0 and int(src_index.max()) < n_src, "src_index out of range"
         # tensors already resident on the device are used in place (no copy, no sync): a pageable host->device copy
         # per call blocks the host until the previous submission has finished
         frames_d, depths_d, mask1_d = self._dev(frames), self._dev(depths), self._dev(mask1)
         M_d = M.to(self.device, torch.float32, non_blocking=True).contiguous()
         si_d = None if src_index is None else src_index.to(self.device, torch.int32).contiguous()
-        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) \
-            | (_lib.TCW_DETERMINISTIC if deterministic else 0)
+        mode = {"window": 0, "integer": _lib.TCW_DETERMINISTIC, "atomic": _lib.TCW_ATOMIC_F32}[accumulation]
+        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) | mode
         odt = torch.float64 if mask else torch.float32
         if out is not None:
             out_frame, out_mask, out_depth, out_flow = out
@@ -177,27 +177,44 @@ class Warper:
                                             _ptr(flag), _ptr(ws), ws.numel(), self._stream())
         _lib.check(rc, "tcw_forward_warp")
         if flag is not None and not lazy_flag:
-            # the reference asserts -1.1 <= warped <= 1.1 before clipping (models/utils.py:580-581)
-            assert int(flag.item()) == 0
+            self.check_status(int(flag.item()))
         return out_frame, out_mask, out_depth, out_flow
 
+    @staticmethod
+    def check_status(status: int) -> None:
+        """Raise for the status bits a call ORs into its flag word (include/tcwarp.h TCW_STATUS_*)."""
+        if status & _lib.TCW_STATUS_SRC_INDEX:
+            raise IndexError("src_index holds a value outside [0, n_src)")
+        # the reference asserts -1.1 <= warped <= 1.1 before clipping (models/utils.py:580-581)
+        assert not (status & _lib.TCW_STATUS_RANGE), "warped colour left [-1.1, 1.1]"
+
     def forward_warp_host(self, frames, depths, M, src_index=None, mask1=None, per_frame_max: bool = True,
-                          mask: bool = False, outputs=None):
+                          mask: bool = False, outputs=None, return_depth: bool = True, return_flow: bool = True,
+                          mask_u8: bool = False):
         """Host-buffer entry (``tcw_forward_warp_host``): CPU float32 tensors in (ideally pinned),
         CPU tensors out; uploads, kernels and downloads are pipelined inside the C library.
         ``M`` is the prepared (n,30) matrix block.  ``outputs`` may carry preallocated pinned
-        (frame, mask, depth, flow) tensors.  Returns (frame, mask, depth, flow, range_flag)."""
+        (frame, mask, depth, flow) tensors.  ``return_depth`` / ``return_flow`` False skip those downloads
+        (every shipped caller drops them: ``warped, mask, _, _``), ``mask_u8`` returns the mask as uint8.
+        Returns (frame, mask, depth, flow, status)."""
         n_src, _, h, w = frames.shape
         n = M.shape[0]
         odt = torch.float64 if mask else torch.float32
+        assert not (mask and mask_u8)
         if outputs is None:
-            outputs = (torch.empty((n, 3, h, w), dtype=odt), torch.empty((n, 1, h, w), dtype=odt),
-                       torch.empty((n, 1, h, w), dtype=torch.float32), torch.empty((n, 2, h, w), dtype=torch.float32))
+            outputs = (torch.empty((n, 3, h, w), dtype=odt),
+                       torch.empty((n, 1, h, w), dtype=torch.uint8 if mask_u8 else odt),
+                       torch.empty((n, 1, h, w), dtype=torch.float32) if return_depth else None,
+                       torch.empty((n, 2, h, w), dtype=torch.float32) if return_flow else None)
         of, om, od, ofl = outputs
+        assert om.dtype == (torch.uint8 if mask_u8 else odt)
         for t in (frames, depths, M):
             assert t.device.type == "cpu" and t.dtype == torch.float32 and t.is_contiguous()
         si = None if src_index is None else src_index.to(torch.int32).contiguous()
-        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0)
+        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) \
+            | (_lib.TCW_HOST_MASK_U8 if mask_u8 else 0)
+        if mask1 is not None:
+            assert mask1.device.type == "cpu" and mask1.dtype == torch.float32 and mask1.is_contiguous()
         flag = ctypes.c_int(0)
         rc = self._lib.tcw_forward_warp_host(self._context(), _ptr(frames), _ptr(mask1), _ptr(depths), _ptr(si),
                                              _ptr(M), n, n_src, h, w, flags, _ptr(of), _ptr(om), _ptr(od), _ptr(ofl),
@@ -321,7 +338,7 @@ class Warper:
                                      _ptr(ws), ws.numel(), self._stream())
         _lib.check(rc, "tcw_splat")
         if is_image:
-            assert int(flag.item()) == 0       # models/utils.py:580-581
+            self.check_status(int(flag.item()))       # models/utils.py:580-581
         if odt == torch.float64:               # float64 inputs (after clean_points) stay float64 in the reference
             out, out_mask = out.double(), out_mask.double()
         return out, out_mask
