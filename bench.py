@@ -29,7 +29,15 @@ ALGO_BYTES_PER_PX = 44.0          # read RGB 12 + depth 4, wri
 N_FRAMES, H, W = 49, 384, 672
 # dram__bytes_read.sum + dram__bytes_write.sum of one k_splat_pair launch from the committed ncu --set full capture
 # (profiles/), for the 24-unit launch shape the roofline figure is quoted on
-NCU_TRAFFIC_BYTES_PER_LAUNCH = 238_216_960   # profiles/r1_final_kernels_full_24units_ncu.txt: 109.06 MB read + 129.16 MB written
+# dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel (ncu --set full, profiles/)
+NCU_TRAFFIC_BYTES_PER_LAUNCH = {"atomic": 238_216_960,   # r1_final_kernels_full_24units_ncu.txt: k_splat_pair, 24 units
+                                "window": None}
+# DRAM bytes of one whole step from the ncu launch list / full captures of the timed schedule (profiles/), per mode
+NCU_DRAM_BYTES_PER_STEP = {"atomic": 3_160_000_000, "window": None}
+# bytes each kernel itself must move per unit pixel (its own inputs + outputs, intermediates included)
+OWN_BYTES_PER_PX = {"window": {"prepass": 16.0, "splat": 44.0, "normalise": 40.0},       # K1: depth in, flow + z' out; K2: flow, z', RGB in, >= 1 slab cell out; K3: >= 1 slab cell in, 20 B out
+                    "atomic": {"prepass": 4.0, "splat": 24.0, "normalise": 40.0},
+                    "integer": {"prepass": 4.0, "splat": 24.0, "normalise": 60.0, "wmax": 16.0}}
 
 
 ACCUMULATION = {"window": "fixed order: warp-private shared-memory windows + ordered gather (default, reproducible)",
@@ -94,14 +102,55 @@ class ClockSampler:
                 "reasons": sorted(self.reasons), "samples": len(self.samples)}
 
 
-def build_workload(seed):
+def build_workload(seed, with_poses=False):
     import torch
     from trajectorycrafter_b200 import prepare_matrices
     from trajectorycrafter_b200.workloads import orbit_units, synthetic_clip
     frames, depths = synthetic_clip(N_FRAMES, H, W, seed=seed)
     T1, T2, K, src = orbit_units(depths, H, W)
     M = prepare_matrices(T1, T2, K)
+    if with_poses:
+        return frames, depths, M, src.to(torch.int32), (T1, T2, K)
     return frames, depths, M, src.to(torch.int32)
+
+
+def host_description():
+    model = "unknown CPU"
+    try:
+        with open("/proc/cpuinfo") as fh:
+            for ln in fh:
+                if ln.startswith("model name"):
+                    model = ln.split(":", 1)[1].strip()
+                    break
+    except OSError:
+        pass
+    return model
+
+
+def reference_torch_throughput(frames, depths, poses, src, unit_ids, threads, deterministic):
+    """Times the reference's OWN torch implementation (oracle/_ref copy of models/utils.py, or /root/reference in the
+    build container) exactly as its callers loop it (demo.py:77-90): Warper(device='cpu'), one forward_warp call per
+    unit with b = 1, mask1 = None, twice = False.  Returns (Mpix/s, seconds)."""
+    import torch
+    from oracle import ref_loader
+    ref = ref_loader.load()
+    T1, T2, K = poses
+    prev_threads, prev_det = torch.get_num_threads(), torch.are_deterministic_algorithms_enabled()
+    torch.set_num_threads(threads)
+    torch.use_deterministic_algorithms(deterministic)
+    try:
+        warper = ref.Warper(device="cpu")
+        s0 = int(src[unit_ids[0]])
+        warper.forward_warp(frames[s0:s0 + 1], None, depths[s0:s0 + 1], T1[:1], T2[:1], K[:1], None, False, twice=False)     # warm-up unit
+        t0 = time.perf_counter()
+        for u in unit_ids:
+            s_ = int(src[u])
+            warper.forward_warp(frames[s_:s_ + 1], None, depths[s_:s_ + 1], T1[u:u + 1], T2[u:u + 1], K[u:u + 1], None, False, twice=False)
+        dt = time.perf_counter() - t0
+    finally:
+        torch.set_num_threads(prev_threads)
+        torch.use_deterministic_algorithms(prev_det)
+    return len(unit_ids) * H * W / dt / 1e6, dt
 
 
 def oracle_throughput(frames, depths, M, src, unit_ids, threads):
@@ -122,32 +171,45 @@ def oracle_throughput(frames, depths, M, src, unit_ids, threads):
 
 
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation of the path, timed on the host cores.
-    The reference is pure Python/torch and cannot travel to the GPU box, so this is the oracle port
-    (kind "port"), threaded over units with every host core."""
+    """--impl reference: the reference's own CPU implementation of the path on the box's host cores.  When the verbatim
+    run-time copy of /root/reference/models/utils.py is present (oracle/_ref/, made by oracle/build_ref.py in the build
+    container; it travels to the GPU box) the UNMODIFIED torch Warper is timed (kind "reference"), looped as demo.py:77-90
+    with every host core; otherwise the C port of the same arithmetic (kind "port").  Each step is a bounded sample of
+    the 392-unit workload: one source frame under the 8 orbit presets, the frame advancing by 6 per step."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
     import oracle
+    from oracle import ref_loader
     oracle.build()
-    frames, depths, M, src = build_workload(1234)
+    frames, depths, M, src, poses = build_workload(1234, with_poses=True)
     threads = os.cpu_count() or 1
-    # bounded sample per step: every 6th frame x 8 presets = 72 of the 392 units
-    unit_ids = [f * 8 + p for f in range(0, N_FRAMES, 6) for p in range(8)]
-    for _ in range(max(1, min(args.warmup, 2))):
-        oracle_throughput(frames, depths, M, src, unit_ids[:threads], threads)
+    use_ref = ref_loader.available()
+
+    def one_step(k):
+        f = (6 * k) % N_FRAMES
+        unit_ids = [f * 8 + p for p in range(8)]
+        if use_ref:
+            return reference_torch_throughput(frames, depths, poses, src, unit_ids, threads, False)[1]
+        return oracle_throughput(frames, depths, M, src, unit_ids, threads)[1]
+
+    for k in range(max(1, min(args.warmup, 3))):
+        one_step(k)
     t0 = time.perf_counter()
-    for _ in range(args.steps):
-        oracle_throughput(frames, depths, M, src, unit_ids, threads)
+    for k in range(args.steps):
+        one_step(k)
     dt = (time.perf_counter() - t0) / args.steps
-    value = len(unit_ids) * H * W / dt / 1e6
-    sample = f"{len(unit_ids)} of 392 units per step (every 6th frame x 8 orbit presets), {threads} threads"
+    value = 8 * H * W / dt / 1e6
+    kind = "reference" if use_ref else "port"
+    sample = (f"8 of 392 units per step (source frame (6*step) mod 49 under the 8 orbit presets, b=1 calls as demo.py:77-90), "
+              f"{threads} threads, {'unmodified torch Warper(device=cpu), default (non-deterministic) scatter' if use_ref else 'C port of the path'}; "
+              f"host: {host_description()}")
     line = {
         "impl": "reference", "metric": "warped_mpix_per_s", "value": value, "unit": "Mpix/s",
         "n_gpus": args.gpus, "steps": args.steps, "warmup": args.warmup, "ms_per_step": dt * 1e3,
         "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
         "config": workload_config(),
-        "cpu_baseline": {"value": value, "unit": "Mpix/s", "cores": threads, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": value, "unit": "Mpix/s", "cores": threads, "kind": kind, "sample": sample},
         "e2e": {"value": value, "unit": "Mpix/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
@@ -274,30 +336,87 @@ def run_ours(args):
     i_ms, i_n, i_units = iso["splat"]
     k_ms, k_n, k_units = prof["splat"]
     if i_n and k_n:
-        # headline: the kernel timed ALONE (pass B) -- a roofline fraction describes one kernel owning the GPU;
-        # "overlapped" repeats the figure for the launches of the timed 4-lane schedule, which share the SMs with
-        # the other lanes' kernels, and "step_frac" is the whole timed step against the same peak
-        def ach(ms_, units_):
-            return ALGO_BYTES_PER_PX * units_ * H * W / (ms_ * 1e-3) / 1e9
+        # roofline.frac is SURVEY 8(d)'s figure: the WHOLE timed step (CUDA events around the batched submission) against
+        # 44 B per warped source pixel.  Beside it: every kernel timed ALONE (one stream, 24-unit launches) against the
+        # bytes that kernel itself must move, and the same kernels inside the timed multi-lane schedule.
+        def gbps(bytes_per_px, ms_, units_):
+            return bytes_per_px * units_ * H * W / (ms_ * 1e-3) / 1e9
         kname = {"window": "k_splat_window", "atomic": "k_splat_pair", "integer": "k_splat_pair_det<i64>"}[args.accumulation]
+        own = OWN_BYTES_PER_PX[args.accumulation]
         tot_i, tot_k = sum(v[0] for v in iso.values()), sum(v[0] for v in prof.values())
-        roofline = {"bound": "hbm", "kernel": kname, "achieved": ach(i_ms, i_units), "peak": peak, "unit": "GB/s",
-                    "frac": ach(i_ms, i_units) / peak, "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH,
-                    "peak_source": peak_src, "avg_launch_us": i_ms / i_n * 1e3, "launches": i_n,
-                    "units_per_launch": i_units / i_n,
-                    "algorithmic_bytes_per_launch": ALGO_BYTES_PER_PX * i_units * H * W / i_n,
+        step_gbps = ALGO_BYTES_PER_PX * px_per_step / (ms_local * 1e-3) / 1e9
+        alone = {}
+        for name, (ms_, n_, units_) in iso.items():
+            if n_:
+                alone[name] = {"ms_per_step": ms_ / iso_steps, "own_bytes_per_px": own.get(name), "avg_launch_us": ms_ / n_ * 1e3,
+                               "achieved_GBps": gbps(own[name], ms_, units_) if own.get(name) else None,
+                               "frac": gbps(own[name], ms_, units_) / peak if own.get(name) else None}
+        roofline = {"bound": "hbm", "kernel": kname, "achieved": step_gbps, "peak": peak, "unit": "GB/s",
+                    "frac": step_gbps / peak, "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH.get(args.accumulation),
+                    "peak_source": peak_src,
+                    "what": "frac / achieved: 44 B x pixels of one step / device time of the whole timed step (all kernels, the timed "
+                            "schedule); kernel_alone: each kernel on one stream in 24-unit launches against its OWN bytes per pixel "
+                            "(outputs larger than L2 there, so its intermediates stream through HBM); in_schedule: the same launches "
+                            "inside the timed multi-lane schedule (they share the SMs, so the times add up to more than the step)",
+                    "algorithmic_bytes_per_step": ALGO_BYTES_PER_PX * px_per_step,
                     "kernel_share_of_step": i_ms / tot_i if tot_i else None,
-                    "per_kernel_ms_per_step": {k: v[0] / iso_steps for k, v in iso.items()},
-                    "how": "CUDA events on the launching stream around every launch, inside bench.py after the timed "
-                           "region; frac/achieved: the kernel alone on the GPU (one stream, 24-unit launches); "
-                           "overlapped: the launches of the timed schedule (4 streams x 3-unit launches run "
-                           "concurrently, so a launch's duration includes sharing the SMs and the per-kernel times add "
-                           "up to more than the step); step_frac: whole timed step",
-                    "overlapped": {"achieved": ach(k_ms, k_units), "frac": ach(k_ms, k_units) / peak,
-                                   "avg_launch_us": k_ms / k_n * 1e3, "launches": k_n, "units_per_launch": k_units / k_n,
-                                   "kernel_share_of_step": k_ms / tot_k if tot_k else None,
-                                   "per_kernel_ms_per_step": {k: v[0] / prof_steps for k, v in prof.items()}},
-                    "step_frac": ALGO_BYTES_PER_PX * px_per_step / (ms_local * 1e-3) / 1e9 / peak}
+                    "kernel_alone": alone,
+                    "kernel_alone_frac": alone.get("splat", {}).get("frac"),
+                    "in_schedule": {"per_kernel_ms_per_step": {k: v[0] / prof_steps for k, v in prof.items()},
+                                    "launches_per_step": sum(v[1] for v in prof.values()) / prof_steps,
+                                    "units_per_launch": k_units / k_n, "kernel_share_of_step": k_ms / tot_k if tot_k else None},
+                    "dram_GBps_actual": (NCU_DRAM_BYTES_PER_STEP[args.accumulation] / (ms_local * 1e-3) / 1e9
+                                         if NCU_DRAM_BYTES_PER_STEP.get(args.accumulation) else None),
+                    "step_frac": step_gbps / peak}
+
+    # ---- the literal metric shape: ONE 49-unit trajectory (49x384x672, preset (0, 30)), inputs resident, device-timed
+    clip49 = None
+    if rank == 0 and not args.no_extras:
+        sel = torch.arange(N_FRAMES, device=dev) * 8 + 1
+        M49, src49 = M_d[sel].contiguous(), src_d[sel].contiguous()
+        out49 = tuple(t[:N_FRAMES] for t in out)
+        for _ in range(5):
+            warper.forward_warp_matrices(frames_d, depths_d, M49, src_index=src49, per_frame_max=True, check_range=flag, out=out49,
+                                         accumulation=args.accumulation)
+        c0, c1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        reps = 40
+        c0.record()
+        for _ in range(reps):
+            warper.forward_warp_matrices(frames_d, depths_d, M49, src_index=src49, per_frame_max=True, check_range=flag, out=out49,
+                                         accumulation=args.accumulation)
+        c1.record()
+        torch.cuda.synchronize()
+        c_ms = c0.elapsed_time(c1) / reps
+        c_px = N_FRAMES * H * W
+        clip49 = {"ms": c_ms, "Mpix_per_s": c_px / (c_ms * 1e-3) / 1e6, "frac": ALGO_BYTES_PER_PX * c_px / (c_ms * 1e-3) / 1e9 / peak,
+                  "what": "one 49-frame trajectory (orbit preset (0, 30)) = 12.6 Mpix per call, 556 MB algorithmic; back-to-back calls "
+                          "re-use 556 MB of buffers, more than the 126 MB L2"}
+
+    # ---- the drop-in entries end to end (ADVICE): device tensors in, fresh outputs, host-side matrix preparation inside
+    dropin = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        from trajectorycrafter_b200.workloads import orbit_units
+        T1, T2, K, _ = orbit_units(depths, H, W, presets=[(0, 30)])
+        f49, d49 = frames_d, depths_d
+        def batch_call():
+            return warper.forward_warp_batch(f49, d49, T1, T2, K, accumulation=args.accumulation)
+        def frame_loop():
+            outs = []
+            for i in range(N_FRAMES):      # the reference's loop, demo.py:77-90
+                outs.append(warper.forward_warp(f49[i:i + 1], None, d49[i:i + 1], T1[i:i + 1], T2[i:i + 1], K[i:i + 1], None))
+            return outs
+        dropin = {}
+        for name, fn in (("forward_warp_batch_49", batch_call), ("forward_warp_b1_loop_49", frame_loop)):
+            fn(); torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(3):
+                r = fn()
+            torch.cuda.synchronize()
+            dt = (time.perf_counter() - t0) / 3
+            dropin[name] = {"ms": dt * 1e3, "Mpix_per_s": N_FRAMES * H * W / dt / 1e6}
+            del r
+        dropin["what"] = ("wall clock incl. the host-side T2*T1^-1 / K^-1 preparation, output allocation and the range-flag read; "
+                          "forward_warp_b1_loop_49 is the reference's own call pattern (49 calls with b = 1)")
 
     # ---- e2e: host buffers through the C-ABI host entry (H2D + kernels + D2H inside the timed region)
     e2e = None
@@ -345,7 +464,7 @@ def run_ours(args):
     # ---- next row of SURVEY.md §8f (N1), reported beside the metric, never part of it: the resize + pack kernel on
     # the reference's own warp resolution, 49 x 576x1024 -> 384x672 (demo.py:91-100,117-120)
     pack = None
-    if rank == 0 and world == 1:
+    if rank == 0 and world == 1 and not args.no_extras:
         Hs, Ws = 576, 1024
         pf = torch.rand((N_FRAMES, 3, Hs, Ws), device=dev) * 2 - 1
         pm = (torch.rand((N_FRAMES, 1, Hs, Ws), device=dev) > 0.2).float()
@@ -364,24 +483,51 @@ def run_ours(args):
                 "note": "includes the two torch.empty output allocations of the Python entry; 462 MB in + 202 MB out, larger than L2"}
         del pf, pm
 
-    # ---- CPU baseline (rank 0, N=1 only): the oracle port on the host cores, one full step once
-    cpu_baseline = None
+    # ---- CPU baseline (rank 0, N=1 only), bounded samples of the same workload on the box's host cores:
+    # the reference's own torch path (oracle/_ref, BASELINE.md section 5: all cores default / deterministic / one thread)
+    # and the C port of the same arithmetic (all cores, one full step)
+    cpu_baseline = cpu_ref = cpu_port = None
     if rank == 0 and world == 1 and not args.no_cpu_baseline:
         import oracle
+        from oracle import ref_loader
         oracle.build()
         threads = os.cpu_count() or 1
         v, secs = oracle_throughput(frames, depths, M, src, list(range(n_units)), threads)
-        cpu_baseline = {"value": v, "unit": "Mpix/s", "cores": threads, "kind": "port",
-                        "sample": f"all 392 units of one step, once ({secs:.1f} s wall on {threads} threads)"}
+        cpu_port = {"value": v, "unit": "Mpix/s", "cores": threads, "kind": "port",
+                    "sample": f"all 392 units of one step, once ({secs:.1f} s wall on {threads} threads)"}
+        cpu_baseline = cpu_port
+        if ref_loader.available():
+            _, _, _, _, poses = build_workload(1234 + rank, with_poses=True)
+            ids = [f * 8 + p for f in (6, 24, 42) for p in range(8)]              # 24 units: 3 source frames x 8 presets
+            v_def, s_def = reference_torch_throughput(frames, depths, poses, src, ids, threads, False)
+            v_det, s_det = reference_torch_throughput(frames, depths, poses, src, ids[:16], threads, True)
+            v_one, s_one = reference_torch_throughput(frames, depths, poses, src, ids[:8], 1, False)
+            cpu_ref = {"value": v_def, "unit": "Mpix/s", "cores": threads, "kind": "reference",
+                       "sample": f"24 of 392 units (source frames 6/24/42 x 8 presets), b=1 calls as demo.py:77-90, {s_def:.1f} s wall",
+                       "modes": {"all_cores_default": {"Mpix_per_s": v_def, "units": 24, "seconds": s_def},
+                                 "all_cores_deterministic": {"Mpix_per_s": v_det, "units": 16, "seconds": s_det},
+                                 "one_thread": {"Mpix_per_s": v_one, "units": 8, "seconds": s_one}},
+                       "host": host_description(), "torch": torch.__version__, "torch_threads": threads,
+                       "what": "the UNMODIFIED reference Warper(device='cpu') (verbatim run-time copy of models/utils.py in oracle/_ref/)"}
+            cpu_baseline = {k: cpu_ref[k] for k in ("value", "unit", "cores", "kind", "sample")}
 
     if rank == 0:
         line = {
             "metric": "warped_mpix_per_s", "value": value, "unit": "Mpix/s", "n_gpus": world,
             "steps": args.steps, "warmup": max(3, args.warmup), "ms_per_step": ms, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": dict(workload_config(), accumulation=ACCUMULATION[args.accumulation], host_enqueue_ms_per_step=round(host_ms, 3)), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
+            "config": workload_config(), "clocks": clocks, "e2e": e2e, "gpu_launches": int(launches),
             "roofline": roofline, "cpu_baseline": cpu_baseline,
+            "details": {"accumulation": ACCUMULATION[args.accumulation], "host_enqueue_ms_per_step": round(host_ms, 3)},
         }
+        if cpu_ref is not None:
+            line["cpu_baseline_reference"] = cpu_ref
+        if cpu_port is not None:
+            line["cpu_baseline_port"] = cpu_port
+        if clip49 is not None:
+            line["clip49"] = clip49
+        if dropin is not None:
+            line["dropin"] = dropin
         if gather is not None:
             line["gather"] = gather
         if per_rank is not None:
@@ -403,6 +549,7 @@ def main():
     ap.add_argument("--accumulation", default="window", choices=sorted(ACCUMULATION))
     ap.add_argument("--no-e2e", action="store_true")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-extras", action="store_true", help="skip the clip49 / drop-in / pack-epilogue legs")
     args = ap.parse_args()
     if args.impl == "reference":
         run_reference(args)

@@ -80,3 +80,46 @@ def assert_depth_close(got, ref, valid, what="depth", rtol=DEPTH_RTOL, count=Non
     bound = rtol + (slack[valid] if isinstance(slack, np.ndarray) else slack)
     assert (rel <= bound).all(), f"{what}: max rel err {rel.max():.3e} > {rtol} on {int((rel > bound).sum())} px"
     return float(rel.max())
+
+
+def parity_report(got, ref_frame, ref_mask, ref_depth, count, got_depth=None):
+    """What the tolerances of a comparison actually rested on: how many output pixels used the crowd slack
+    (> MANY contributions) and the worst colour / depth error among the pixels that did NOT."""
+    got = np.asarray(got, dtype=np.float64)
+    ref = np.asarray(ref_frame, dtype=np.float64)
+    err = np.abs(got - ref) / np.maximum(1.0, np.abs(ref))
+    crowded = np.zeros(ref_mask.shape, bool) if count is None else (np.asarray(count) > MANY)
+    plain = ~np.broadcast_to(crowded, err.shape)
+    rep = {"px": int(ref_mask.size), "slack_px": int(crowded.sum()), "colour_worst_unslacked": float(err[plain].max()) if plain.any() else 0.0,
+           "colour_worst": float(err.max())}
+    if got_depth is not None:
+        valid = (np.asarray(ref_mask) > 0)
+        gd, rd = np.asarray(got_depth, dtype=np.float64), np.asarray(ref_depth, dtype=np.float64)
+        rel = np.zeros(rd.shape)
+        rel[valid] = np.abs(gd[valid] - rd[valid]) / np.maximum(np.abs(rd[valid]), 1e-30)
+        sel = valid & ~crowded
+        rep["depth_worst_unslacked"] = float(rel[sel].max()) if sel.any() else 0.0
+        rep["depth_worst"] = float(rel.max())
+    return rep
+
+
+def sha_digest(a):
+    """SHA-256 of an array's bytes with -0.0 folded into +0.0 (as oracle/gen_golden_config1.py stores them)."""
+    import hashlib
+    a = np.ascontiguousarray(a) + np.zeros((), dtype=np.asarray(a).dtype)
+    return np.frombuffer(hashlib.sha256(a.tobytes()).digest(), dtype=np.uint8).copy()
+
+
+def block_mean(a, k=8):
+    a = np.asarray(a)
+    n, c, h, w = a.shape
+    return a.astype(np.float64).reshape(n, c, h // k, k, w // k, k).mean(axis=(3, 5))
+
+
+def load_config1():
+    """tests/golden/config1_p7.npz -> (frames (3,3,384,672) f32, depths (3,1,384,672) f32, dict of the rest)."""
+    import torch
+    z = np.load(os.path.join(GOLDEN_DIR, "config1_p7.npz"))
+    frames = torch.from_numpy(z["frames_u8"].astype(np.float32) / 255.0).permute(0, 3, 1, 2).contiguous() * 2.0 - 1.0
+    depths = torch.from_numpy(z["depth_f16"].astype(np.float32)).unsqueeze(1).contiguous()
+    return frames, depths, {k: z[k] for k in z.files if k not in ("frames_u8", "depth_f16")}

@@ -4,7 +4,7 @@ import pytest
 import torch
 
 import oracle
-from _util import assert_colour_close, assert_depth_close, bit_equal, warp_case_names
+from _util import assert_colour_close, assert_depth_close, bit_equal, parity_report, warp_case_names
 from trajectorycrafter_b200 import Warper, prepare_matrices
 from trajectorycrafter_b200.workloads import ORBIT_PRESETS, orbit_units, ring_cameras, synthetic_clip
 
@@ -35,6 +35,8 @@ def check_against(got, ref_frame, ref_mask, ref_depth, ref_flow, tol=1e-5):
         count = oracle.contrib_count(ref_flow)      # widens the tolerance only where > 64 contributions meet
     e1 = assert_colour_close(gf, ref_frame, tol=tol, count=count)
     e2 = assert_depth_close(gd, ref_depth, ref_mask, rtol=tol, count=count)
+    # what the comparison rested on: pixels that used the crowd slack, worst error among those that did not
+    print("parity:", parity_report(gf, ref_frame, ref_mask, ref_depth, count, got_depth=gd))
     return e1, e2
 
 

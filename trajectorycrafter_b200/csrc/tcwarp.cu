@@ -401,8 +401,9 @@ static void win_layout(const tcw_ctx* ctx, int n_units, int h, int w, int flags,
     L->o_flow = take((size_t)L->P * 2 * hw * sizeof(float));
     L->o_off = take((size_t)L->S * L->nh * sizeof(int));
     L->o_pile = take((size_t)L->S * L->ns * 8 * sizeof(float));
-    L->o_pool4 = take((size_t)L->S * L->pool_cells * sizeof(float4));
-    L->o_poolw = take((size_t)L->S * L->pool_cells * sizeof(float));
+    // each pool array is followed by 256 B of zeros: cell S * pool_cells is the "nothing here" cell of the branch-free gather
+    L->o_pool4 = take((size_t)L->S * L->pool_cells * sizeof(float4) + 256);
+    L->o_poolw = take((size_t)L->S * L->pool_cells * sizeof(float) + 256);
     L->o_spill4 = take((size_t)L->S * hw * sizeof(float4));
     L->o_spillw = take((size_t)L->S * hw * sizeof(float));
     L->o_tmp = (flags & TCW_CLEAN) ? take((size_t)L->S * 4 * hw * sizeof(float)) : 0;      // fp32 colour + mask ahead of clean_points
@@ -438,7 +439,7 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
     A.box = (WinBox*)(ws + L.o_box); A.grp = (WinGrp*)(ws + L.o_grp);
     A.zbuf = (float*)(ws + L.o_z); A.flowbuf = (float*)(ws + L.o_flow);
     A.slab_off = (int*)(ws + L.o_off); A.pile = (float*)(ws + L.o_pile);
-    A.pool4 = (float4*)(ws + L.o_pool4); A.poolw = (float*)(ws + L.o_poolw); A.pool_cells = L.pool_cells;
+    A.pool4 = (float4*)(ws + L.o_pool4); A.poolw = (float*)(ws + L.o_poolw); A.pool_cells = L.pool_cells; A.n_slots = L.S;
     A.spill4 = (float4*)(ws + L.o_spill4); A.spillw = (float*)(ws + L.o_spillw);
     A.status = J.range_flag;
     float* tmp = clean ? (float*)(ws + L.o_tmp) : nullptr;
@@ -447,6 +448,8 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
     if (rc) return rc;
 
     CUDA_TRY(cudaMemsetAsync(workspace, 0, L.hdr, st));                                       // per-unit stats
+    CUDA_TRY(cudaMemsetAsync(ws + L.o_pool4 + (size_t)L.S * L.pool_cells * sizeof(float4), 0, 256, st));      // the zero cells behind the pools
+    CUDA_TRY(cudaMemsetAsync(ws + L.o_poolw + (size_t)L.S * L.pool_cells * sizeof(float), 0, 256, st));
     // shared planes: all zero on entry (k_gather_normalise re-zeroes what it read)
     const int S_used = L.S < n_units ? L.S : n_units;
     CUDA_TRY(cudaMemsetAsync(ws + L.o_spill4, 0, (size_t)S_used * hw * sizeof(float4), st));
@@ -457,8 +460,8 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
         for (int a = 0; a < nu; a += 65535) {
             const int na = nu - a < 65535 ? nu - a : 65535;
             prof_begin(ctx, PK_ZMAX, na, s);
-            if (A.fused) k_win_prepass<true><<<dim3(g1.x, na), WIN_GROUP * 32, 0, s>>>(A, u0 + a, prep0 + a, slot0 < 0 ? -1 : slot0 + a);
-            else k_win_prepass<false><<<dim3(g1.x, na), WIN_GROUP * 32, 0, s>>>(A, u0 + a, prep0 + a, slot0 < 0 ? -1 : slot0 + a);
+            if (A.fused) k_win_prepass<true><<<dim3(g1.x, na), WIN_PRE_WARPS * 32, 0, s>>>(A, u0 + a, prep0 + a, slot0 < 0 ? -1 : slot0 + a);
+            else k_win_prepass<false><<<dim3(g1.x, na), WIN_PRE_WARPS * 32, 0, s>>>(A, u0 + a, prep0 + a, slot0 < 0 ? -1 : slot0 + a);
             prof_end(ctx, s);
             LAUNCH_CHECK("k_win_prepass");
         }

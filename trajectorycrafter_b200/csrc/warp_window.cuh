@@ -22,13 +22,15 @@
 #define TCW_WIN_CAP 768            // cells of shared-memory window per warp (both half-strips together)
 #endif
 constexpr int WIN_CAP = TCW_WIN_CAP;
-constexpr int WIN_P4 = WIN_CAP + WIN_CAP / 8 + 1;            // float4 slots: one pad slot per 8 cells (stride-2 lanes stay conflict-free)
-constexpr int WIN_PW = WIN_CAP + WIN_CAP / 32 + 1;           // float slots: one pad word per 32 cells
+constexpr int WIN_SCRATCH = 32;                               // scratch cells behind the window: one per lane, for pixels that add nothing
+constexpr int WIN_P4 = (WIN_CAP + WIN_SCRATCH) + (WIN_CAP + WIN_SCRATCH) / 8 + 1;      // float4 slots: one pad slot per 8 cells (stride-2 lanes stay conflict-free)
+constexpr int WIN_PW = WIN_P4;                                // float slots: the weight plane uses the float4 plane's padded index
 constexpr int WIN_BYTES = ((WIN_P4 * 16 + WIN_PW * 4 + WIN_CAP) + 15) / 16 * 16;
 constexpr int WIN_WARPS = 4;                                 // warps (strips) per CTA of K2
 constexpr int WIN_GROUP = 8;                                 // half-strips per K1 CTA = per box group
+constexpr int WIN_PRE_WARPS = WIN_GROUP / 2;                 // K1: one warp per 64 x 8 strip = two half-strips
 constexpr int WIN_POOL_MULT = 3;                             // slab pool of a unit: WIN_POOL_MULT * h * w cells
-constexpr int WIN_MAXC = 256;                                // candidate half-strips one K3 CTA holds at a time
+constexpr int WIN_MAXC = 64;                                 // candidate slabs one K3 warp lists at a time
 
 struct WinBox { short x0, y0, bw, bh; int flags, pad; };     // cropped target coords; bw == 0: no cell.  flags bit 0: has pile pixels
 struct WinGrp { int x0, y0, x1, y1; };                       // union of WIN_GROUP boxes, [x0, x1) x [y0, y1); x1 <= x0: empty
@@ -46,7 +48,7 @@ struct WinArgs {
     float* flowbuf; float* zbuf; WinBox* box; WinGrp* grp;   // per prep slot
     // K2 products
     int* counter; int* spill_flag; int* slab_off; float* pile;   // per splat slot
-    float4* pool4; float* poolw; long long pool_cells;
+    float4* pool4; float* poolw; long long pool_cells; int n_slots;
     float4* spill4; float* spillw;
     int* status;                                             // device word: bit 1 = a footprint was reduced into the shared plane, bit 2 = src_index out of range
 };
@@ -64,7 +66,7 @@ __device__ __forceinline__ int win_src(const WinArgs& A, int u) {
 // PROJECT = false (generic splat): flow and depth are inputs; only the boxes and the normaliser are computed.
 // ------------------------------------------------------------------------------------------------
 template <bool PROJECT>
-__global__ void __launch_bounds__(WIN_GROUP * 32)
+__global__ void __launch_bounds__(WIN_PRE_WARPS * 32)
 k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
     constexpr unsigned FULL = 0xffffffffu;
     __shared__ int gb[4];
@@ -75,19 +77,21 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
     if (threadIdx.x == 0) { gb[0] = INT_MAX; gb[1] = INT_MAX; gb[2] = INT_MIN; gb[3] = INT_MIN; }
     if (blockIdx.x == 0 && threadIdx.x == 0 && slot0 >= 0) { A.counter[slot0 + uc] = 0; A.spill_flag[slot0 + uc] = 0; }
     __syncthreads();
-    const int hs = blockIdx.x * WIN_GROUP + wv;
-    int xmin = INT_MAX, ymin = INT_MAX, xmax = INT_MIN, ymax = INT_MIN;
+    const int strip = blockIdx.x * WIN_PRE_WARPS + wv;
+    // box of this lane's pixels in float (floor / ceil are monotone: the box of the floats gives the box of the cells)
+    const float INF = __int_as_float(0x7f800000);
+    float bx0 = INF, by0 = INF, bx1 = -INF, by1 = -INF;
     bool pile = false;
     float zs = 0.0f;
-    if (hs < A.nh) {
-        const int hpr = 2 * A.strips_x;
-        const int sy = hs / hpr, hx = hs - sy * hpr;
-        const int x = hx * 32 + lane;
-        const bool ok = x < w;
-        const int xc = ok ? x : 0;
+    if (strip < A.ns) {
+        const int sy = strip / A.strips_x, sx = strip - sy * A.strips_x;
+        const int xA = sx * 64 + 2 * lane, xB = xA + 1;
+        const bool okA = xA < w, okB = xB < w;
+        const int cA = okA ? xA : 0, cB = okB ? xB : 0;
         const int y0 = sy * 8, y1 = y0 + 8 < h ? y0 + 8 : h;
         const int s = PROJECT ? win_src(A, u) : u;
-        const float fx = (float)x;
+        const float fxA = (float)xA, fxB = (float)xB;
+        const u64 fx2 = pk(fxA, fxB);
         const float wf1 = (float)(w + 1), hf1 = (float)(h + 1);
         const float* __restrict__ dp = A.depth + (size_t)s * hw;
         float* __restrict__ flp = nullptr;
@@ -95,7 +99,8 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
         const float* __restrict__ gfl = nullptr;
         float m[9], T[12], K[9];
         bool PIN = false;
-        float u0_pin = 0.f, a0 = 0.f, a1 = 0.f, a2 = 0.f;
+        u64 u0p = 0;
+        float a0A = 0.f, a1A = 0.f, a2A = 0.f, a0B = 0.f, a1B = 0.f, a2B = 0.f;
         if (PROJECT) {
             flp = A.flow_out ? A.flow_out + (size_t)u * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
             zp = A.zbuf + (size_t)ps * hw;
@@ -109,23 +114,28 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
             // pinhole zero pattern of K1^-1 and K2: the dropped terms are products with an exact 0 (see warp_pair.cuh)
             PIN = m[1] == 0.0f && m[3] == 0.0f && m[6] == 0.0f && m[7] == 0.0f && m[8] == 1.0f &&
                   K[1] == 0.0f && K[3] == 0.0f && K[6] == 0.0f && K[7] == 0.0f && K[8] == 1.0f;
-            a0 = __fmul_rn(m[0], fx); a1 = __fmul_rn(m[3], fx); a2 = __fmul_rn(m[6], fx);
-            u0_pin = __fadd_rn(a0, m[2]);
+            a0A = __fmul_rn(m[0], fxA); a1A = __fmul_rn(m[3], fxA); a2A = __fmul_rn(m[6], fxA);
+            a0B = __fmul_rn(m[0], fxB); a1B = __fmul_rn(m[3], fxB); a2B = __fmul_rn(m[6], fxB);
+            u0p = pk(__fadd_rn(a0A, m[2]), __fadd_rn(a0B, m[2]));
         } else {
             gfl = A.gflow + (size_t)u * 2 * hw;
         }
-        for (int y = y0; y < y1; y += 2) {
-            const bool rowB = y + 1 < y1;
-            const float fyA = (float)y, fyB = (float)(y + 1);
-            const size_t qA = (size_t)y * w + xc, qB = rowB ? qA + w : qA;
+        // float2 accesses when both pixels exist in every lane that has any, rows stay 8-byte aligned
+        const bool vec2 = __all_sync(FULL, okB || !okA) && !(w & 1) &&
+            !((((size_t)dp) | ((size_t)flp) | ((size_t)zp) | ((size_t)gfl)) & 7);
+        for (int y = y0; y < y1; ++y) {
+            const float fy = (float)y;
+            const size_t qA = (size_t)y * w + cA, qB = (size_t)y * w + cB;
             float flxA, flxB, flyA, flyB, zA, zB;
             if (PROJECT) {
-                const float dA = __ldg(dp + qA), dB = __ldg(dp + qB);
+                float dA, dB;
+                if (vec2) { const float2 t = __ldg((const float2*)(dp + qA)); dA = t.x; dB = t.y; }
+                else { dA = __ldg(dp + qA); dB = __ldg(dp + qB); }
                 float P0A, P1A, P2A, P0B, P1B, P2B, Y2A, Y2B;
                 if (PIN) {
-                    const float u1A = __fadd_rn(__fmul_rn(m[4], fyA), m[5]), u1B = __fadd_rn(__fmul_rn(m[4], fyB), m[5]);
+                    const float u1 = __fadd_rn(__fmul_rn(m[4], fy), m[5]);
                     const u64 d2 = pk(dA, dB);
-                    const u64 X0 = mul2(d2, pk1(u0_pin)), X1 = mul2(d2, pk(u1A, u1B));
+                    const u64 X0 = mul2(d2, u0p), X1 = mul2(d2, pk1(u1));
                     float a, b, c, e, f, g;
                     upk(mul2(X0, pk1(T[0])), a, b); upk(mul2(X1, pk1(T[1])), c, e); upk(mul2(d2, pk1(T[2])), f, g);
                     const float Y0A = __fadd_rn(__fadd_rn(__fadd_rn(a, c), f), T[3]), Y0B = __fadd_rn(__fadd_rn(__fadd_rn(b, e), g), T[3]);
@@ -142,10 +152,10 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
                 } else {
                     #pragma unroll
                     for (int k = 0; k < 2; ++k) {
-                        const float d = k ? dB : dA, fy = k ? fyB : fyA;
-                        const float u0 = __fadd_rn(__fadd_rn(a0, __fmul_rn(m[1], fy)), m[2]);
-                        const float u1 = __fadd_rn(__fadd_rn(a1, __fmul_rn(m[4], fy)), m[5]);
-                        const float u2 = __fadd_rn(__fadd_rn(a2, __fmul_rn(m[7], fy)), m[8]);
+                        const float d = k ? dB : dA;
+                        const float u0 = __fadd_rn(__fadd_rn(k ? a0B : a0A, __fmul_rn(m[1], fy)), m[2]);
+                        const float u1 = __fadd_rn(__fadd_rn(k ? a1B : a1A, __fmul_rn(m[4], fy)), m[5]);
+                        const float u2 = __fadd_rn(__fadd_rn(k ? a2B : a2A, __fmul_rn(m[7], fy)), m[8]);
                         const float X0 = __fmul_rn(d, u0), X1 = __fmul_rn(d, u1), X2 = __fmul_rn(d, u2);
                         const float Y0 = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[0], X0), __fmul_rn(T[1], X1)), __fmul_rn(T[2], X2)), T[3]);
                         const float Y1 = __fadd_rn(__fadd_rn(__fadd_rn(__fmul_rn(T[4], X0), __fmul_rn(T[5], X1)), __fmul_rn(T[6], X2)), T[7]);
@@ -174,51 +184,68 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
                         qy = pk(__fdiv_rn(P1A, P2A), __fdiv_rn(P1B, P2B));
                     }
                 }
-                upk(sub2(qx, pk1(fx)), flxA, flxB);
-                upk(sub2(qy, pk(fyA, fyB)), flyA, flyB);
+                const u64 flx2 = sub2(qx, fx2), fly2 = sub2(qy, pk1(fy));
+                upk(flx2, flxA, flxB);
+                upk(fly2, flyA, flyB);
                 zA = P2A; zB = P2B;
-                if (ok) {
-                    __stcg(flp + qA, flxA); __stcg(flp + hw + qA, flyA); __stcg(zp + qA, zA);
-                    if (rowB) { __stcg(flp + qB, flxB); __stcg(flp + hw + qB, flyB); __stcg(zp + qB, zB); }
+                if (vec2) {
+                    if (okA) {
+                        __stcg((float2*)(flp + qA), make_float2(flxA, flxB)); __stcg((float2*)(flp + hw + qA), make_float2(flyA, flyB));
+                        __stcg((float2*)(zp + qA), make_float2(zA, zB));
+                    }
+                } else {
+                    if (okA) { __stcg(flp + qA, flxA); __stcg(flp + hw + qA, flyA); __stcg(zp + qA, zA); }
+                    if (okB) { __stcg(flp + qB, flxB); __stcg(flp + hw + qB, flyB); __stcg(zp + qB, zB); }
                 }
             } else {
-                flxA = __ldg(gfl + qA); flyA = __ldg(gfl + hw + qA); zA = __ldg(dp + qA);
-                flxB = __ldg(gfl + qB); flyB = __ldg(gfl + hw + qB); zB = __ldg(dp + qB);
-            }
-            #pragma unroll
-            for (int k = 0; k < 2; ++k) {
-                if (!ok || (k && !rowB)) continue;
-                const float z = k ? zB : zA;
-                zs = fmaxf(zs, clampf(z, 0.0f, 1000.0f));
-                // same arithmetic as K2 (models/utils.py:450-452): off = (flow + grid) + 1
-                const float ox = __fadd_rn(__fadd_rn(k ? flxB : flxA, fx), 1.0f), oy = __fadd_rn(__fadd_rn(k ? flyB : flyA, k ? fyB : fyA), 1.0f);
-                if (ox == 2.0f && oy == 2.0f && w >= 2 && h >= 2) { pile = true; continue; }
-                if (!(ox > 0.0f && ox < wf1 && oy > 0.0f && oy < hf1)) continue;      // every corner in the pad ring
-                const float f0x = floorf(ox), f0y = floorf(oy);
-                const int ix0 = (int)f0x, iy0 = (int)f0y;
-                const int ix1 = ix0 + (ox != f0x ? 1 : 0), iy1 = iy0 + (oy != f0y ? 1 : 0);
-                const int xl = ix0 > 1 ? ix0 : 1, xh = ix1 < w ? ix1 : w, yl = iy0 > 1 ? iy0 : 1, yh = iy1 < h ? iy1 : h;
-                if (xl <= xh && yl <= yh) {
-                    xmin = min(xmin, xl - 1); xmax = max(xmax, xh - 1);
-                    ymin = min(ymin, yl - 1); ymax = max(ymax, yh - 1);
+                if (vec2) {
+                    const float2 f0 = __ldg((const float2*)(gfl + qA)), f1 = __ldg((const float2*)(gfl + hw + qA)), z2 = __ldg((const float2*)(dp + qA));
+                    flxA = f0.x; flxB = f0.y; flyA = f1.x; flyB = f1.y; zA = z2.x; zB = z2.y;
+                } else {
+                    flxA = __ldg(gfl + qA); flyA = __ldg(gfl + hw + qA); zA = __ldg(dp + qA);
+                    flxB = __ldg(gfl + qB); flyB = __ldg(gfl + hw + qB); zB = __ldg(dp + qB);
                 }
             }
+            // same arithmetic as K2 (models/utils.py:450-452): off = (flow + grid) + 1
+            float oxA, oxB, oyA, oyB;
+            upk(add2(add2(pk(flxA, flxB), fx2), pk1(1.0f)), oxA, oxB);
+            upk(add2(add2(pk(flyA, flyB), pk1(fy)), pk1(1.0f)), oyA, oyB);
+            if (okA) zs = fmaxf(zs, zA);
+            if (okB) zs = fmaxf(zs, zB);
+            const bool inA = okA && oxA > 0.0f && oxA < wf1 && oyA > 0.0f && oyA < hf1;      // else: every corner in the pad ring
+            const bool inB = okB && oxB > 0.0f && oxB < wf1 && oyB > 0.0f && oyB < hf1;
+            const bool pA = inA && oxA == 2.0f && oyA == 2.0f && w >= 2 && h >= 2;
+            const bool pB = inB && oxB == 2.0f && oyB == 2.0f && w >= 2 && h >= 2;
+            pile |= pA | pB;
+            if (inA && !pA) { bx0 = fminf(bx0, oxA); bx1 = fmaxf(bx1, oxA); by0 = fminf(by0, oyA); by1 = fmaxf(by1, oyA); }
+            if (inB && !pB) { bx0 = fminf(bx0, oxB); bx1 = fmaxf(bx1, oxB); by0 = fminf(by0, oyB); by1 = fmaxf(by1, oyB); }
         }
     }
-    xmin = __reduce_min_sync(FULL, xmin); ymin = __reduce_min_sync(FULL, ymin);
-    xmax = __reduce_max_sync(FULL, xmax); ymax = __reduce_max_sync(FULL, ymax);
-    const bool anyp = __any_sync(FULL, pile);
+    // cells a pixel at (ox, oy) touches: floor .. ceil, clipped to the real cells 1 .. w / 1 .. h; in cropped coordinates
+    // [max(floor(ox), 1) - 1, min(ceil(ox), w) - 1]
+    int xmin = INT_MAX, ymin = INT_MAX, xmax = INT_MIN, ymax = INT_MIN;
+    if (bx1 >= bx0) {
+        xmin = max((int)floorf(bx0), 1) - 1; xmax = min((int)ceilf(bx1), w) - 1;
+        ymin = max((int)floorf(by0), 1) - 1; ymax = min((int)ceilf(by1), h) - 1;
+        if (xmin > xmax || ymin > ymax) { xmin = INT_MAX; ymin = INT_MAX; xmax = INT_MIN; ymax = INT_MIN; }
+    }
+    // lanes 0-15 hold the left half-strip (columns 0-31 of the strip), lanes 16-31 the right one
+    const unsigned hm = lane < 16 ? 0x0000ffffu : 0xffff0000u;
+    xmin = __reduce_min_sync(hm, xmin); ymin = __reduce_min_sync(hm, ymin);
+    xmax = __reduce_max_sync(hm, xmax); ymax = __reduce_max_sync(hm, ymax);
+    const bool anyp = __ballot_sync(FULL, pile) & hm;
+    zs = clampf(zs, 0.0f, 1000.0f);                                                 // clamp is monotone: once, after the max
     const unsigned zbits = __reduce_max_sync(FULL, __float_as_uint(zs));          // zs >= 0: uint order == float order
+    if ((lane & 15) == 0 && strip < A.ns) {
+        WinBox b;
+        const bool some = xmax >= xmin;
+        b.x0 = some ? (short)xmin : 0; b.y0 = some ? (short)ymin : 0;
+        b.bw = some ? (short)(xmax - xmin + 1) : 0; b.bh = some ? (short)(ymax - ymin + 1) : 0;
+        b.flags = anyp ? 1 : 0; b.pad = 0;
+        A.box[(size_t)ps * A.nh + 2 * strip + (lane >> 4)] = b;
+        if (some) { atomicMin(&gb[0], xmin); atomicMin(&gb[1], ymin); atomicMax(&gb[2], xmax + 1); atomicMax(&gb[3], ymax + 1); }
+    }
     if (lane == 0) {
-        if (hs < A.nh) {
-            WinBox b;
-            const bool some = xmax >= xmin;
-            b.x0 = some ? (short)xmin : 0; b.y0 = some ? (short)ymin : 0;
-            b.bw = some ? (short)(xmax - xmin + 1) : 0; b.bh = some ? (short)(ymax - ymin + 1) : 0;
-            b.flags = anyp ? 1 : 0; b.pad = 0;
-            A.box[(size_t)ps * A.nh + hs] = b;
-            if (some) { atomicMin(&gb[0], xmin); atomicMin(&gb[1], ymin); atomicMax(&gb[2], xmax + 1); atomicMax(&gb[3], ymax + 1); }
-        }
         // log is monotone: one log per warp.  The polynomial K2 evaluates per pixel, so ld / L == 1 at the arg-max pixel
         const float ld = log1x(__fadd_rn(1.0f, __uint_as_float(zbits)));
         atomicMax(&A.stats_rw[u].lbits, __float_as_uint(ld));
@@ -265,7 +292,7 @@ __device__ __forceinline__ void emit_window(const WinOut& o, int lane, int id, u
     }
     bool pend = id >= 0;
     if (!__any_sync(FULL, pend)) return;
-    const int p4 = id + (id >> 3), pw = id + (id >> 5);
+    const int p4 = id + (id >> 3), pw = p4;
     do {
         if (pend) o.tag[id] = (unsigned char)lane;
         __syncwarp();
@@ -285,6 +312,29 @@ template <int MODE>
 __device__ __forceinline__ void emit_window_single(const WinOut& o, int lane, bool take, int id, u64 rg, u64 bz, float w) {
     const u64 w2 = pk1(w);
     emit_window<MODE>(o, lane, take ? id : -1, mul2(rg, w2), mul2(bz, w2), w);
+}
+
+
+// One corner of one pixel column set, WM_SMEM fast path: the caller has established that no two lanes address the
+// same cell in this step (win_steps_distinct), so the update is a plain read-modify-write of the warp's own window.
+__device__ __forceinline__ void win_step(const WinOut& o, bool on, int id, u64 rg, u64 bz, float w) {
+    if (on) {
+        const int p4 = id + (id >> 3);
+        const float4 a = o.s4[p4];
+        const float s = o.sw[p4];
+        const u64 w2 = pk1(w);
+        float r, g, b, z;
+        upk(fma2(rg, w2, pk(a.x, a.y)), r, g); upk(fma2(bz, w2, pk(a.z, a.w)), b, z);
+        o.s4[p4] = make_float4(r, g, b, z);
+        o.sw[p4] = s + w;
+    }
+    __syncwarp();
+}
+// live lanes form one run of consecutive lanes?
+__device__ __forceinline__ bool win_run(unsigned m) {
+    if (m == 0u) return true;
+    const unsigned t = m >> (__ffs(m) - 1);
+    return (t & (t + 1u)) == 0u;
 }
 
 // per-unit source pointers of a strip
@@ -407,8 +457,20 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
 
         int idNWA, idSWA, idNEA, idSEA, idNWB, idSWB, idNEB, idSEB;
         u64 wNW2, wSW2, wNE2, wSE2;
+        bool distinct = false;      // WM_SMEM: every step of this row addresses 32 different cells (or none)
         if (!general) {
             const bool dxA = oxA != fx0A, dxB = oxB != fx0B, dyA = oyA != fy0A, dyB = oyB != fy0B;   // ceil == floor + 1 ?
+            if (MODE == WM_SMEM) {
+                // Pixels A of all lanes are one step, pixels B another.  Two lanes of a step share a cell only if they
+                // share its column: with k = 2 ix0 + (ix1 - ix0), left and right columns both grow strictly from lane
+                // l-1 to lane l  <=>  k_l - k_{l-1} >= 2; live lanes must be one run so that neighbours are enough.
+                const unsigned mA = __ballot_sync(FULL, liveA), mB = __ballot_sync(FULL, liveB);
+                const int kA = 2 * ix0A + (dxA ? 1 : 0), kB = 2 * ix0B + (dxB ? 1 : 0);
+                const int qA = __shfl_up_sync(FULL, kA, 1), qB = __shfl_up_sync(FULL, kB, 1);
+                const unsigned below = lane ? (1u << (lane - 1)) : 0u;
+                const bool bad = (liveA && (mA & below) && kA - qA < 2) || (liveB && (mB & below) && kB - qB < 2);
+                distinct = win_run(mA) && win_run(mB) && !__any_sync(FULL, bad);
+            }
             const u64 fx02 = pk(fx0A, fx0B), fy02 = pk(fy0A, fy0B);
             const u64 fx12 = pk(dxA ? fx0A + 1.0f : fx0A, dxB ? fx0B + 1.0f : fx0B);
             const u64 fy12 = pk(dyA ? fy0A + 1.0f : fy0A, dyB ? fy0B + 1.0f : fy0B);
@@ -440,6 +502,14 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
         }
         float wNWA, wNWB, wSWA, wSWB, wNEA, wNEB, wSEA, wSEB;
         upk(wNW2, wNWA, wNWB); upk(wSW2, wSWA, wSWB); upk(wNE2, wNEA, wNEB); upk(wSE2, wSEA, wSEB);
+        if (MODE == WM_SMEM && distinct) {
+            // eight plain steps in a fixed order: NW, SW, NE, SE of the A pixels and of the B pixels
+            win_step(o, liveA, idNWA, rgA, bzA, wNWA); win_step(o, liveB, idNWB, rgB, bzB, wNWB);
+            win_step(o, liveA, idSWA, rgA, bzA, wSWA); win_step(o, liveB, idSWB, rgB, bzB, wSWB);
+            win_step(o, liveA, idNEA, rgA, bzA, wNEA); win_step(o, liveB, idNEB, rgB, bzB, wNEB);
+            win_step(o, liveA, idSEA, rgA, bzA, wSEA); win_step(o, liveB, idSEB, rgB, bzB, wSEB);
+            continue;
+        }
 
         // ---- register-level merge (the rules of warp_pair.cuh without the row carries: the window adds across rows).
         // Destinations: Lt / Lb = pixel A's left cells, Mt / Mb = pixel B's left cells.  Sources: the left lane's B
@@ -494,6 +564,185 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
         emit_window<MODE>(o, lane, idSWA, Lbrg, Lbbz, Lbw);
         emit_window<MODE>(o, lane, sT ? -1 : idNWB, Mtrg, Mtbz, Mtw);
         emit_window<MODE>(o, lane, sB ? -1 : idSWB, Mbrg, Mbbz, Mbw);
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// The forward warp's rows in a shared-memory window, lean form.  A row takes the eight plain steps (win_step without
+// the branch) when every pixel of the warp is either "interior" (all four corner cells are real cells) or plainly
+// outside, no pixel sits exactly on padded cell (2,2), and each step addresses 32 different cells; any other row is
+// handed to splat_window_rows (clamped formulas, serialised additions).  Pixels that add nothing go through the same
+// steps with weight 0 into a scratch slot of their own lane (`dummy` + lane), so the row has no divergent branch.
+// Rows are loaded one ahead (two register sets, the loop body is written twice).
+// ------------------------------------------------------------------------------------------------
+struct WinRow { float2 fx, fy, z, r, g, b, m; };      // .x = pixel A (column x0 + 2 lane), .y = pixel B
+
+// loads the compiler may not sink below later volatile statements (the shared-memory steps): a row's loads are issued
+// one row ahead of their use
+__device__ __forceinline__ float2 ld2_cg(const float* p) {
+    float2 v;
+    asm volatile("ld.global.cg.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float2 ld2_nc(const float* p) {
+    float2 v;
+    asm volatile("ld.global.nc.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ld1_cg(const float* p) {
+    float v;
+    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+__device__ __forceinline__ float ld1_nc(const float* p) {
+    float v;
+    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
+    return v;
+}
+
+__device__ __forceinline__ void splat_rows_fused(const WinArgs& A, const WinSrc& S, const WinOut& o, int lane, int x0s, int y0, int y1,
+                                                 bool act, int pitch, int idbase, int cells, float L,
+                                                 u64& hrg, u64& hbz, float& hwt, bool& any_pile) {
+    constexpr unsigned FULL = 0xffffffffu;
+    const int h = A.h, w = A.w;
+    const int xA = x0s + 2 * lane, xB = xA + 1;
+    const bool okA = xA < w && act, okB = xB < w && act;
+    const unsigned hw32 = (unsigned)((size_t)h * w);
+    const u64 fx2 = pk((float)xA, (float)xB), one2 = pk1(1.0f);
+    const int colA = xA < w ? xA : 0, colB = xB < w ? xB : 0;
+    const bool vec2 = xB < w && !(w & 1) &&
+        !((((size_t)S.fl) | ((size_t)S.wd) | ((size_t)S.v[0]) | ((size_t)S.v[1]) | ((size_t)S.v[2]) | ((size_t)S.m1)) & 7);
+    const bool vec2all = __all_sync(FULL, vec2 || !(xA < w));
+    const bool has_m = S.m1 != nullptr;
+    const bool Lok = L >= 9.5367431640625e-07f;
+    float rL = rcp_approx(L);
+    rL = fmaf(rL, fmaf(-L, rL, 1.0f), rL);
+    const u64 rL2 = pk1(rL), nL2 = pk1(-L);
+    const unsigned below = lane ? (1u << (lane - 1)) : 0u;
+    const unsigned s4b = (unsigned)__cvta_generic_to_shared(o.s4), swb = (unsigned)__cvta_generic_to_shared(o.sw);
+    const int dummy_id = cells + lane;
+
+    auto load_row = [&](WinRow& R, int y) {
+        const unsigned q = (unsigned)y * (unsigned)w;
+        if (vec2all) {
+            const unsigned qa = q + colA;
+            R.fx = ld2_cg(S.fl + qa); R.fy = ld2_cg(S.fl + hw32 + qa); R.z = ld2_cg(S.wd + qa);
+            R.r = ld2_nc(S.v[0] + qa); R.g = ld2_nc(S.v[1] + qa); R.b = ld2_nc(S.v[2] + qa);
+            if (has_m) R.m = ld2_nc(S.m1 + qa);
+        } else {
+            const unsigned qa = q + colA, qb = q + colB;
+            R.fx = make_float2(ld1_cg(S.fl + qa), ld1_cg(S.fl + qb)); R.fy = make_float2(ld1_cg(S.fl + hw32 + qa), ld1_cg(S.fl + hw32 + qb));
+            R.z = make_float2(ld1_cg(S.wd + qa), ld1_cg(S.wd + qb));
+            R.r = make_float2(ld1_nc(S.v[0] + qa), ld1_nc(S.v[0] + qb)); R.g = make_float2(ld1_nc(S.v[1] + qa), ld1_nc(S.v[1] + qb));
+            R.b = make_float2(ld1_nc(S.v[2] + qa), ld1_nc(S.v[2] + qb));
+            if (has_m) R.m = make_float2(ld1_nc(S.m1 + qa), ld1_nc(S.m1 + qb));
+        }
+    };
+    // the top and the bottom cell of one column of one pixel: two reads, two writes.  The two cells differ (the caller
+    // sends the bottom one to the scratch slot when the pixel sits on a cell row exactly), and no other lane addresses
+    // either of them in this step.
+    auto step2 = [&](int idT, int idB, u64 rg, u64 bz, float wT, float wB) {
+        const int pT = idT + (idT >> 3), pB = idB + (idB >> 3);
+        const unsigned awT = swb + 4u * (unsigned)pT, a4T = s4b + 16u * (unsigned)pT;
+        const unsigned awB = swb + 4u * (unsigned)pB, a4B = s4b + 16u * (unsigned)pB;
+        float4 a, c;
+        float sa, sc;
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(a4T));
+        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w) : "r"(a4B));
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sa) : "r"(awT));
+        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sc) : "r"(awB));
+        const u64 t2 = pk1(wT), b2 = pk1(wB);
+        float r, g, b, z;
+        upk(fma2(rg, t2, pk(a.x, a.y)), r, g); upk(fma2(bz, t2, pk(a.z, a.w)), b, z);
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(a4T), "f"(r), "f"(g), "f"(b), "f"(z) : "memory");
+        upk(fma2(rg, b2, pk(c.x, c.y)), r, g); upk(fma2(bz, b2, pk(c.z, c.w)), b, z);
+        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(a4B), "f"(r), "f"(g), "f"(b), "f"(z) : "memory");
+        asm volatile("st.shared.f32 [%0], %1;" :: "r"(awT), "f"(sa + wT) : "memory");
+        asm volatile("st.shared.f32 [%0], %1;" :: "r"(awB), "f"(sc + wB) : "memory");
+        __syncwarp();
+    };
+    // returns false when the row needs the general routine
+    auto row = [&](const WinRow& R, int y) -> bool {
+        const float fy = (float)y;
+        float oxA, oxB, oyA, oyB;
+        upk(add2(add2(pk(R.fx.x, R.fx.y), fx2), one2), oxA, oxB);
+        upk(add2(add2(pk(R.fy.x, R.fy.y), pk1(fy)), one2), oyA, oyB);
+        const float fx0A = floorf(oxA), fx0B = floorf(oxB), fy0A = floorf(oyA), fy0B = floorf(oyB);
+        const int ix0A = (int)fx0A, ix0B = (int)fx0B, iy0A = (int)fy0A, iy0B = (int)fy0B;
+        // interior: floor cell and its +1 neighbours are real cells (1 .. w, 1 .. h); far: even the floor cell is outside the padded grid
+        const bool inA = okA && (unsigned)(ix0A - 1) < (unsigned)(w - 1) && (unsigned)(iy0A - 1) < (unsigned)(h - 1);
+        const bool inB = okB && (unsigned)(ix0B - 1) < (unsigned)(w - 1) && (unsigned)(iy0B - 1) < (unsigned)(h - 1);
+        const bool farA = !okA || (unsigned)ix0A > (unsigned)w || (unsigned)iy0A > (unsigned)h || !(oxA == oxA) || !(oyA == oyA);
+        const bool farB = !okB || (unsigned)ix0B > (unsigned)w || (unsigned)iy0B > (unsigned)h || !(oxB == oxB) || !(oyB == oyB);
+        const bool dxA = oxA != fx0A, dxB = oxB != fx0B, dyA = oyA != fy0A, dyB = oyB != fy0B;       // ceil == floor + 1 ?
+        const bool pileA = inA && (ix0A | iy0A) == 2 && !dxA && !dyA, pileB = inB && (ix0B | iy0B) == 2 && !dxB && !dyB;
+        bool slow = (!inA && !farA) || (!inB && !farB) || pileA || pileB;
+        const unsigned mA = __ballot_sync(FULL, inA), mB = __ballot_sync(FULL, inB);
+        {   // distinct columns per step (see splat_window_rows): k = 2 ix0 + (ix1 - ix0) grows by >= 2 from live lane to live lane
+            const int kA = 2 * ix0A + (dxA ? 1 : 0), kB = 2 * ix0B + (dxB ? 1 : 0);
+            const int qA = __shfl_up_sync(FULL, kA, 1), qB = __shfl_up_sync(FULL, kB, 1);
+            slow |= (inA && (mA & below) && kA - qA < 2) || (inB && (mB & below) && kB - qB < 2);
+        }
+        if (__any_sync(FULL, slow) || !win_run(mA) || !win_run(mB)) return false;
+        if ((mA | mB) == 0u) return true;                                                  // nothing lands anywhere
+        // ---- soft-z weight mg = mask1 * exp(-50 * log(1 + sat(z)) / L)   (:490-513)
+        u64 mg2;
+        {
+            const u64 ld = log2x(add2(pk(clampf(R.z.x, 0.0f, 1000.0f), clampf(R.z.y, 0.0f, 1000.0f)), one2));
+            u64 qd;
+            if (Lok) qd = div2_with_rcp(ld, nL2, rL2);
+            else qd = pk(__fdiv_rn(plo(ld), L), __fdiv_rn(phi(ld), L));
+            mg2 = exp2x(mul2(qd, pk1(-50.0f)));
+            if (has_m) mg2 = mul2(mg2, pk(R.m.x, R.m.y));
+        }
+        mg2 = pk(inA ? plo(mg2) : 0.0f, inB ? phi(mg2) : 0.0f);
+        // ---- proximity weights (:477-488)
+        const u64 ox2 = pk(oxA, oxB), oy2 = pk(oyA, oyB), fx02 = pk(fx0A, fx0B), fy02 = pk(fy0A, fy0B);
+        const u64 fx12 = add2(fx02, pk(dxA ? 1.0f : 0.0f, dxB ? 1.0f : 0.0f)), fy12 = add2(fy02, pk(dyA ? 1.0f : 0.0f, dyB ? 1.0f : 0.0f));
+        const u64 ax = sub2(one2, sub2(ox2, fx02)), bx = sub2(one2, sub2(fx12, ox2));
+        const u64 ay = sub2(one2, sub2(oy2, fy02)), by = sub2(one2, sub2(fy12, oy2));
+        float wNWA, wNWB, wSWA, wSWB, wNEA, wNEB, wSEA, wSEB;
+        upk(mul2(mul2(ay, ax), mg2), wNWA, wNWB); upk(mul2(mul2(by, ax), mg2), wSWA, wSWB);
+        upk(mul2(mul2(ay, bx), mg2), wNEA, wNEB); upk(mul2(mul2(by, bx), mg2), wSEA, wSEB);
+        // ---- cells.  A pixel that adds nothing uses its lane's scratch slot; so does the bottom cell of a pixel that
+        // sits exactly on a cell row (top and bottom cell are the same cell there: the top one takes both weights)
+        const bool tA = inA && dyA, tB = inB && dyB;
+        const int nwA = inA ? iy0A * pitch + ix0A + idbase : dummy_id, nwB = inB ? iy0B * pitch + ix0B + idbase : dummy_id;
+        const int swA = tA ? nwA + pitch : dummy_id, swB = tB ? nwB + pitch : dummy_id;
+        const int eA = inA && dxA ? 1 : 0, eB = inB && dxB ? 1 : 0;
+        if (!tA) { wNWA += wSWA; wNEA += wSEA; wSWA = 0.0f; wSEA = 0.0f; }
+        if (!tB) { wNWB += wSWB; wNEB += wSEB; wSWB = 0.0f; wSEB = 0.0f; }
+        const u64 rgA = pk(R.r.x, R.g.x), bzA = pk(R.b.x, R.z.x), rgB = pk(R.r.y, R.g.y), bzB = pk(R.b.y, R.z.y);
+        step2(nwA, swA, rgA, bzA, wNWA, wSWA);
+        step2(nwB, swB, rgB, bzB, wNWB, wSWB);
+        step2(nwA + eA, tA ? swA + eA : dummy_id, rgA, bzA, wNEA, wSEA);
+        step2(nwB + eB, tB ? swB + eB : dummy_id, rgB, bzB, wNEB, wSEB);
+        return true;
+    };
+
+    WinRow R0, R1;
+    R0.m = make_float2(1.f, 1.f); R1.m = R0.m;
+    load_row(R0, y0);
+    {   // the window is cleared while the first row's loads are in flight
+        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+        const int n4 = cells + (cells >> 3) + 1;
+        for (int i = lane; i < n4; i += 32) o.s4[i] = z4;
+        for (int i = lane; i < n4; i += 32) o.sw[i] = 0.f;
+        __syncwarp();
+    }
+    unsigned later = 0u;                                   // rows left to the general routine, run after the others
+    for (int y = y0; y < y1; y += 2) {
+        if (y + 1 < y1) load_row(R1, y + 1);
+        if (!row(R0, y)) later |= 1u << (y - y0);
+        if (y + 1 < y1) {
+            if (y + 2 < y1) load_row(R0, y + 2);
+            if (!row(R1, y + 1)) later |= 1u << (y + 1 - y0);
+        }
+    }
+    while (later) {
+        const int k = __ffs(later) - 1;
+        later &= later - 1;
+        splat_window_rows<WM_SMEM>(A, S, o, lane, x0s, y0 + k, y0 + k + 1, act, pitch, idbase, L, hrg, hbz, hwt, any_pile);
     }
 }
 
@@ -578,17 +827,20 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
             }
             const int pitch_l = shared_plane ? w : pitch;
             if (mode == WM_SMEM) {
-                const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-                const int n4 = cells + (cells >> 3) + 1, nw = cells + (cells >> 5) + 1;
-                for (int i = lane; i < n4; i += 32) o.s4[i] = z4;
-                for (int i = lane; i < nw; i += 32) o.sw[i] = 0.f;
-                __syncwarp();
-                splat_window_rows<WM_SMEM>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
+                if (!A.fused) {
+                    const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
+                    const int n4 = cells + (cells >> 3) + 1, nw = n4;
+                    for (int i = lane; i < n4; i += 32) o.s4[i] = z4;
+                    for (int i = lane; i < nw; i += 32) o.sw[i] = 0.f;
+                    __syncwarp();
+                }
+                if (A.fused) splat_rows_fused(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, cells, L, hrg, hbz, hwt, any_pile);
+                else splat_window_rows<WM_SMEM>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
                 __syncwarp();
                 // the window becomes a dense slab (cells in window order == slab order)
                 for (int i = lane; i < cells; i += 32) {
                     __stcg(o.g4 + i, o.s4[i + (i >> 3)]);
-                    __stcg(o.gw + i, o.sw[i + (i >> 5)]);
+                    __stcg(o.gw + i, o.sw[i + (i >> 3)]);
                 }
                 __syncwarp();
             } else {
@@ -640,15 +892,18 @@ struct WinNormArgs {
 __global__ void __launch_bounds__(128)
 k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, int tiles_x) {
     constexpr unsigned FULL = 0xffffffffu;
-    __shared__ int cand[WIN_MAXC];
-    __shared__ int ncand, scan_pos;
+    __shared__ int4 cand_all[4][WIN_MAXC];                          // per warp: {x0, y0, bw | bh << 16, slab offset}
     const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    int4* cand = cand_all[wv];
+    __shared__ int hitl_all[4][32];
+    int* hitl = hitl_all[wv];
     const int uc = blockIdx.y, u = unit0 + uc, ps = prep0 + uc, sl = slot0 + uc;
     const int h = A.h, w = A.w;
     const size_t hw = (size_t)h * w;
     const int ty_t = blockIdx.x / tiles_x, tx_t = blockIdx.x - ty_t * tiles_x;
-    const int X0 = tx_t * 32, Y0 = ty_t * 32, X1 = X0 + 32 < w ? X0 + 32 : w, Y1 = Y0 + 32 < h ? Y0 + 32 : h;
+    const int X0 = tx_t * 32, Y0 = ty_t * 32, X1 = X0 + 32 < w ? X0 + 32 : w;
     const int tx = X0 + lane, row0 = Y0 + wv * 8;
+    const int R1 = row0 + 8 < h ? row0 + 8 : h;                     // this warp's tile: [X0, X1) x [row0, R1)
     const WinBox* __restrict__ box = A.box + (size_t)ps * A.nh;
     const WinGrp* __restrict__ grp = A.grp + (size_t)ps * A.ng;
     const int* __restrict__ soff = A.slab_off + (size_t)sl * A.nh;
@@ -660,59 +915,71 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
     #pragma unroll
     for (int r = 0; r < 8; ++r) { acc[r] = make_float4(0.f, 0.f, 0.f, 0.f); accw[r] = 0.f; }
 
-    if (threadIdx.x == 0) scan_pos = 0;
-    __syncthreads();
-    while (true) {
-        // ---- warp 0: next batch of overlapping half-strips, ascending
-        if (wv == 0) {
-            int n = 0, g = scan_pos;              // scan_pos counts half-strips already examined (multiple of WIN_GROUP except at the end)
-            while (g < A.nh && n + 32 * WIN_GROUP <= WIN_MAXC) {
-                // 32 groups per step
-                const int gi = g / WIN_GROUP + lane;
-                bool hit = false;
-                if (gi < A.ng) { const WinGrp q = grp[gi]; hit = q.x0 < X1 && q.x1 > X0 && q.y0 < Y1 && q.y1 > Y0; }
-                unsigned hits = __ballot_sync(FULL, hit);
-                while (hits) {
-                    const int k = __ffs(hits) - 1;
-                    hits &= hits - 1;
-                    const int hsb = (g / WIN_GROUP + k) * WIN_GROUP;
-                    bool in = false;
-                    if (lane < WIN_GROUP && hsb + lane < A.nh) {
-                        const WinBox b = box[hsb + lane];
-                        in = b.bw > 0 && b.x0 < X1 && b.x0 + b.bw > X0 && b.y0 < Y1 && b.y0 + b.bh > Y0 && soff[hsb + lane] >= 0;
-                    }
-                    const unsigned m = __ballot_sync(FULL, in);
-                    if (in) cand[n + __popc(m & ((1u << lane) - 1))] = hsb + lane;
-                    n += __popc(m);
-                }
-                g += 32 * WIN_GROUP;
-            }
-            if (lane == 0) { ncand = n; scan_pos = g; }
-        }
-        __syncthreads();
-        const int n = ncand;
-        const bool more = scan_pos < A.nh;
-        // ---- every warp: add the listed slabs to its 32 x 8 cells
+    // adds the n listed slabs (ascending half-strip order) to this warp's 32 x 8 cells.  Branch-free: a cell outside
+    // the slab reads the zero cell behind the pools, so all sixteen loads of a slab are in flight together and every
+    // accumulator takes the same sequence of additions (x + 0 changes nothing).
+    const unsigned zero_cell = (unsigned)((long long)(A.n_slots - sl) * A.pool_cells);
+    const char* __restrict__ b4 = (const char*)p4;
+    const char* __restrict__ b1 = (const char*)pw;
+    auto add_listed = [&](int n) {
+        __syncwarp();
         for (int i = 0; i < n; ++i) {
-            const int hs = cand[i];
-            const WinBox b = box[hs];
-            const int off = soff[hs];
-            const int ry0 = b.y0 > row0 ? b.y0 : row0, ry1 = (b.y0 + b.bh) < (row0 + 8) ? (b.y0 + b.bh) : (row0 + 8);
-            if (ry0 >= ry1) continue;                                     // warp-uniform
-            const bool colin = tx >= b.x0 && tx < b.x0 + b.bw;
-            const int cbase = off + (row0 - b.y0) * b.bw + (tx - b.x0);
+            const int4 e = cand[i];
+            const int bw = e.z & 0xffff, bh = (int)((unsigned)e.z >> 16);
+            const int c = tx - e.x, r0 = row0 - e.y;
+            const bool colin = (unsigned)c < (unsigned)bw;
+            int ci = e.w + r0 * bw + c;
+            float4 s4[8];
+            float sw[8];
             #pragma unroll
             for (int r = 0; r < 8; ++r) {
-                if (row0 + r >= ry0 && row0 + r < ry1 && colin) {
-                    const int ci = cbase + r * b.bw;
-                    const float4 s = __ldcg(p4 + ci);
-                    const float sw = __ldcg(pw + ci);
-                    acc[r].x += s.x; acc[r].y += s.y; acc[r].z += s.z; acc[r].w += s.w; accw[r] += sw;
-                }
+                const unsigned cu = ((unsigned)(r0 + r) < (unsigned)bh && colin) ? (unsigned)ci : zero_cell;
+                s4[r] = __ldcg((const float4*)(b4 + (size_t)cu * 16u));
+                sw[r] = __ldcg((const float*)(b1 + (size_t)cu * 4u));
+                ci += bw;
+            }
+            #pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                acc[r].x += s4[r].x; acc[r].y += s4[r].y; acc[r].z += s4[r].z; acc[r].w += s4[r].w; accw[r] += sw[r];
             }
         }
-        __syncthreads();
-        if (!more) break;
+        __syncwarp();
+    };
+
+    if (row0 < h) {
+        // ---- every warp lists the half-strips whose box overlaps its own tile, ascending: 32 box groups per round,
+        // then the boxes of up to four hit groups per step (lane = group-in-step * 8 + half-strip-in-group)
+        int n = 0;
+        const int sel = lane >> 3, j = lane & 7;
+        for (int g0 = 0; g0 < A.ng; g0 += 32) {
+            const int gi = g0 + lane;
+            bool hit = false;
+            if (gi < A.ng) { const WinGrp q = grp[gi]; hit = q.x0 < X1 && q.x1 > X0 && q.y0 < R1 && q.y1 > row0; }
+            const unsigned hits = __ballot_sync(FULL, hit);
+            const int nhit = __popc(hits);
+            if (nhit == 0) continue;
+            __syncwarp();
+            if (hit) hitl[__popc(hits & ((1u << lane) - 1u))] = gi;          // hit groups, ascending
+            __syncwarp();
+            for (int b = 0; b < nhit; b += 4) {
+                if (n > WIN_MAXC - 32) { add_listed(n); n = 0; }
+                bool in = false;
+                int4 e = make_int4(0, 0, 0, 0);
+                if (b + sel < nhit) {
+                    const int hs = hitl[b + sel] * WIN_GROUP + j;
+                    if (hs < A.nh) {
+                        const WinBox bx = box[hs];
+                        const int off = soff[hs];
+                        in = bx.bw > 0 && off >= 0 && bx.x0 < X1 && bx.x0 + bx.bw > X0 && bx.y0 < R1 && bx.y0 + bx.bh > row0;
+                        e = make_int4(bx.x0, bx.y0, (int)bx.bw | ((int)bx.bh << 16), off);
+                    }
+                }
+                const unsigned m = __ballot_sync(FULL, in);
+                if (in) cand[n + __popc(m & ((1u << lane) - 1u))] = e;
+                n += __popc(m);
+            }
+        }
+        add_listed(n);
     }
     // ---- the unit's shared plane (only when a footprint did not fit the slab pool); re-zeroed for the next unit
     if (A.spill_flag[sl]) {
@@ -749,28 +1016,31 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
     }
     // ---- normalise, mask, clip (models/utils.py:571-583)
     bool bad = false;
-    if (tx < w) {
+    if (tx < w && row0 < h) {
+        const size_t p0 = (size_t)row0 * w + tx;
+        float* o0 = N.out_frame + (size_t)u * N.out_c * hw + p0;
+        float* om = N.out_mask + (size_t)u * hw + p0;
+        float* od = N.out_depth ? N.out_depth + (size_t)u * hw + p0 : nullptr;
+        const float hole = N.is_image ? -1.0f : 0.0f;
         #pragma unroll
         for (int r = 0; r < 8; ++r) {
-            const int ty = row0 + r;
-            if (ty >= h) break;
-            const size_t p = (size_t)ty * w + tx;
+            if (row0 + r >= h) break;
             const float W = accw[r];
             const bool valid = W > 0.0f;
             float rr = rcp_approx(W);
             rr = fmaf(rr, fmaf(-W, rr, 1.0f), rr);
-            float v[4] = {acc[r].x * rr, acc[r].y * rr, acc[r].z * rr, acc[r].w * rr};
-            const float hole = N.is_image ? -1.0f : 0.0f;
+            const float v[4] = {acc[r].x * rr, acc[r].y * rr, acc[r].z * rr, acc[r].w * rr};
             #pragma unroll
             for (int c = 0; c < 4; ++c) {
                 if (c < N.out_c) {
                     float x = valid ? v[c] : hole;
                     if (N.is_image) { bad |= !(fabsf(x) <= 1.1f); x = clampf(x, -1.0f, 1.0f); }
-                    __stcs(N.out_frame + ((size_t)u * N.out_c + c) * hw + p, x);
+                    __stcs(o0 + (size_t)c * hw, x);
                 }
             }
-            __stcs(N.out_mask + (size_t)u * hw + p, valid ? 1.0f : 0.0f);
-            if (N.out_depth) __stcs(N.out_depth + (size_t)u * hw + p, valid ? v[3] : 0.0f);
+            __stcs(om, valid ? 1.0f : 0.0f);
+            if (od) { __stcs(od, valid ? v[3] : 0.0f); od += w; }
+            o0 += w; om += w;
         }
     }
     if (bad && N.range_flag) atomicOr(N.range_flag, 1);
