@@ -114,6 +114,24 @@ def build_workload(seed, with_poses=False):
     return frames, depths, M, src.to(torch.int32)
 
 
+def bind_to_gpu_cpus(index):
+    """Restrict this process to the CPUs NVML reports as local to GPU `index` (ranks of one box otherwise all pin their host
+    buffers on NUMA node 0 and share its memory controllers).  Returns the CPU list, or None if NVML cannot tell."""
+    try:
+        import pynvml
+        pynvml.nvmlInit()
+        hnd = pynvml.nvmlDeviceGetHandleByIndex(index)
+        words = pynvml.nvmlDeviceGetCpuAffinity(hnd, (os.cpu_count() + 63) // 64)
+        cpus = [64 * i + b for i, wd in enumerate(words) for b in range(64) if (int(wd) >> b) & 1]
+        cpus = [c for c in cpus if c in os.sched_getaffinity(0)]
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return [cpus[0], cpus[-1], len(cpus)]
+    except Exception:
+        pass
+    return None
+
+
 def host_description():
     model = "unknown CPU"
     try:
@@ -236,6 +254,7 @@ def run_ours(args):
         raise SystemExit("bench.py needs a CUDA device: this path has no CPU fallback")
     torch.cuda.set_device(local)
     dev = torch.device("cuda", local)
+    numa = bind_to_gpu_cpus(local) if world > 1 else None      # pinned host buffers are first-touched on the GPU's own NUMA node
     if world > 1:
         os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
         dist.init_process_group("nccl", device_id=dev)
@@ -441,25 +460,82 @@ def run_ours(args):
                "api": "Warper.forward_warp_host -> tcw_forward_warp_host (pinned host buffers)"}
         del houts
 
-    # ---- the path's one exchange step: gather colour+mask of one 49-unit trajectory per rank on rank 0
-    gather = None
+    # ---- multi-GPU as the path is specified: ONE clip's 392 units sharded over the ranks (strong scaling), then the same
+    # with the exchange inside the timed step -- colour float32 + mask uint8 (13 B per pixel) of ALL units on rank 0:
+    # (a) one NCCL gather of per-rank packed buffers the warp writes directly, (b) the fused form: every rank's gather
+    # kernel stores straight into rank 0's buffer through peer-mapped memory (no collective, no local copy)
+    strong = with_gather = None
     if world > 1:
-        from trajectorycrafter_b200.sharding import gather_condition_video
-        n_g = N_FRAMES
-        col, msk = out[0][:n_g].contiguous(), out[1][:n_g].contiguous()
-        for _ in range(2):
-            gather_condition_video(col, msk, n_g * world, dst=0)
+        from trajectorycrafter_b200.sharding import (PeerBuffer, gather_packed, local_sources, packed_buffer, packed_views,
+                                                     shard_bounds, unpack_gathered)
+        sf, sd, sM, ssrc = build_workload(1234)                       # the same clip on every rank
+        n_all = sM.shape[0]
+        lo, hi = shard_bounds(n_all, world, rank)
+        nl = hi - lo
+        needed, lsrc = local_sources(ssrc, lo, hi)                    # a rank uploads only the source frames its units read
+        sf_d, sd_d = sf[needed].contiguous().to(dev), sd[needed].contiguous().to(dev)
+        sM_d, ss_d = sM[lo:hi].contiguous().to(dev), lsrc.to(dev)
+        o_depth, o_flow = torch.empty((nl, 1, H, W), device=dev), torch.empty((nl, 2, H, W), device=dev)
+        o_col, o_msk = torch.empty((nl, 3, H, W), device=dev), torch.empty((nl, 1, H, W), device=dev)
+        packed = packed_buffer(nl, H, W, dev)
+        p_col, p_msk = packed_views(packed, nl, H, W)
+        peer = PeerBuffer(warper, n_all, H, W, dst=0)
+        r_col, r_msk = peer.views(lo, hi)
+
+        def warp_into(col, msk, u8):
+            warper.forward_warp_matrices(sf_d, sd_d, sM_d, src_index=ss_d, per_frame_max=True, check_range=flag,
+                                         out=(col, msk, o_depth, o_flow), mask_u8=u8)
+
+        def timed(fn, steps):
+            for _ in range(3):
+                fn()
+            barrier()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(steps):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            barrier()
+            return max_over_ranks(a.elapsed_time(b) / steps)
+
+        ksteps = max(1, args.steps)
+        ms_strong = timed(lambda: warp_into(o_col, o_msk, False), ksteps)
+        gathered = [None]
+        def nccl_step():
+            warp_into(p_col, p_msk, True)
+            gathered[0] = gather_packed(packed, n_all, H, W, dst=0)
+        ms_nccl = timed(nccl_step, ksteps)
+        ms_peer = timed(lambda: warp_into(r_col, r_msk, True), ksteps)
+        # the assembled clip on rank 0 must equal what one GPU computes for the whole clip, bit for bit (fixed summation order)
+        same = None
+        if rank == 0:
+            pick = torch.tensor([0, n_all // 2 - 1, n_all // 2, n_all - 1])
+            ref_c, ref_m, _, _ = warper.forward_warp_matrices(sf.to(dev), sd.to(dev), sM[pick].to(dev), src_index=ssrc[pick].to(dev),
+                                                              per_frame_max=True, check_range=flag, mask_u8=True)
+            parts = unpack_gathered(gathered[0], n_all, H, W)
+            g_col = torch.cat([p_[0] for p_ in parts])[pick.to(dev)]
+            same = bool(torch.equal(peer.colour[pick.to(dev)], ref_c) and torch.equal(peer.mask[pick.to(dev)], ref_m)
+                        and torch.equal(g_col, ref_c))
+        wire = 13 * (n_all - n_all // world) * H * W
+        px_all = n_all * H * W
+        strong = {"value": px_all / (ms_strong * 1e-3) / 1e6, "unit": "Mpix/s", "ms": ms_strong, "units_per_rank": nl,
+                  "what": "config 2's 392 units of ONE clip sharded over the ranks, outputs left on each rank, no collective"}
+        with_gather = {"value": px_all / (ms_peer * 1e-3) / 1e6, "unit": "Mpix/s", "ms": ms_peer,
+                       "ingress_GBps": wire / (ms_peer * 1e-3) / 1e9, "bytes_into_rank0": wire,
+                       "nvlink_bound_ms": wire / 770e9 * 1e3,
+                       "how": "fused: the gather kernel of every rank stores colour f32 + mask u8 (13 B/px) straight into rank 0's "
+                              "buffer (CUDA IPC peer mapping over NVLink / NVSwitch); the step ends when all ranks' kernels have finished",
+                       "nccl_single_gather": {"value": px_all / (ms_nccl * 1e-3) / 1e6, "ms": ms_nccl,
+                                              "ingress_GBps": wire / (ms_nccl * 1e-3) / 1e9,
+                                              "how": "warp into a per-rank packed buffer, then ONE dist.gather of 13 B/px"},
+                       "assembled_equals_single_gpu_bits": same}
+        if rank != 0:
+            peer.close()          # unmap before the owner frees
         barrier()
-        g0, g1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
-        g0.record()
-        for _ in range(5):
-            gather_condition_video(col, msk, n_g * world, dst=0)
-        g1.record()
-        torch.cuda.synchronize()
-        g_ms = max_over_ranks(g0.elapsed_time(g1) / 5)
-        wire = n_g * H * W * 13 * (world - 1)
-        gather = {"ms": g_ms, "bytes_into_rank0": wire, "ingress_GBps": wire / (g_ms * 1e-3) / 1e9,
-                  "what": "NCCL gather of colour f32 + mask u8 (13 B/px) of 49 units per rank to rank 0"}
+        if rank == 0:
+            peer.close()
+    gather = None
 
     # ---- next row of SURVEY.md §8f (N1), reported beside the metric, never part of it: the resize + pack kernel on
     # the reference's own warp resolution, 49 x 576x1024 -> 384x672 (demo.py:91-100,117-120)
@@ -528,8 +604,11 @@ def run_ours(args):
             line["clip49"] = clip49
         if dropin is not None:
             line["dropin"] = dropin
-        if gather is not None:
-            line["gather"] = gather
+        if strong is not None:
+            line["strong"] = strong
+            line["with_gather"] = with_gather
+        if numa is not None:
+            line["details"]["cpu_affinity_first_last_count"] = numa
         if per_rank is not None:
             line["per_rank"] = per_rank
         if pack is not None:

@@ -37,6 +37,10 @@ extern "C" {
 #define TCW_ATOMIC_F32    16   /* tcw_forward_warp: opt-in float reductions into L2 accumulators (the round-1 kernel); the order of the
                                   additions, and with it the last bits of colour / depth, varies from run to run */
 #define TCW_HOST_MASK_U8  32   /* tcw_forward_warp_host only: out_mask is a uint8 (n,1,h,w) host buffer (0 / 1), a quarter of the download */
+#define TCW_MASK_U8       64   /* tcw_forward_warp (default mode, no TCW_CLEAN): out_mask is a uint8 (n,1,h,w) DEVICE buffer (0 / 1).  With
+                                  out_frame / out_mask pointing into a peer GPU's memory (tcw_ipc_open) this is the fused form of the
+                                  exchange that assembles the condition video on the denoiser's rank: 13 B per pixel over NVLink,
+                                  stored by the gather kernel itself (the consumer is reference demo.py:117-148) */
 
 /* bits of *range_flag (status word) */
 #define TCW_STATUS_RANGE       1   /* a valid colour left [-1.1, 1.1] before the clamp: the reference's assert (models/utils.py:580-581) */
@@ -133,6 +137,56 @@ int tcw_clean_points(tcw_ctx* ctx, const float* frame, const float* mask2, int c
  */
 int tcw_resize_pack(tcw_ctx* ctx, const float* frame, const float* mask, int n, int H, int W, int h, int w,
                     float* out_video, float* out_masks, void* cuda_stream);
+
+/*
+ * The fork's global point-cloud renderer (reference notebooks/06_10_25_vggt/warper_point_cloud.py, GlobalPointCloudWarper).
+ * tcw_pc_lift              lift_to_3d_pointcloud (:12-77): frame (b,3,h,w), mask1 (b,1,h,w)|NULL, depth (b,1,h,w),
+ *                          Minv (b,21) DEVICE = K^-1 (9) | rows 0..2 of T^-1 (12) -> out_points, out_colors (b,h,w,3), both * mask1.
+ *                          step > 1: the inputs are a ::step subsample and pixel (x, y) stands for (x*step, y*step) -- with the
+ *                          extrinsic itself in the T slot this is VisualizationWarper.extract_3d_points_with_colors
+ *                          (notebooks/28_08_25_trajectories/core.py:15-79)
+ * tcw_pc_render_zbuffer    render_pointcloud_zbuffer_vectorized_point_size (:522-646): points / colors (N,3) DEVICE, camera =
+ *                          21 HOST floats (rows 0..2 of the target extrinsic | intrinsic); every point's point_size footprint,
+ *                          (point_size 0 = render_pointcloud_zbuffer_vectorized :445-519: one pixel, clamped into the image),
+ *                          nearest entry per pixel (64-bit atomicMin on depth bits | reversed entry index: bit-reproducible);
+ *                          out_frame (3,h,w) with -1 in empty pixels, out_mask (h,w), out_depth (h,w)|NULL; workspace >= h*w*8 B
+ * tcw_pc_render_bilinear   render_from_camera(use_bilinear=True) (:158-256, :351-443), one camera: depth-weighted bilinear
+ *                          scatter (float reductions: tolerance parity); weights (N) DEVICE; workspace >= 256 + h*w*16 B
+ */
+int tcw_pc_lift(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth, const float* Minv,
+                int b, int h, int w, int step, float* out_points, float* out_colors, void* cuda_stream);
+int tcw_pc_render_zbuffer(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                          long long n_points, int h, int w, int point_size,
+                          float* out_frame, float* out_mask, float* out_depth,
+                          void* workspace, size_t workspace_bytes, void* cuda_stream);
+int tcw_pc_render_bilinear(tcw_ctx* ctx, const float* points, const float* colors, const float* weights, const float* camera,
+                           long long n_points, int h, int w, float depth_threshold,
+                           float* out_frame, float* out_mask, void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/*
+ * The step right before the warp, on the device (reference models/infer.py:79-92, the numpy / torch lines that end
+ * DepthCrafterDemo.infer, and the radius of demo.py:539-543):
+ *   res (n,h,w,c) float32 = the depth model's raw output (c = 3 channels-last as the pipeline returns it, or 1)
+ *   out_depth (n,1,h,w) = clip(10000 * (1 / max(3900 * (mean_c(res) - min) / (max - min), 1e-5)), near, far), bit-identical
+ *                         (torch evaluates `10000.0 / t` as t.reciprocal() * 10000.0)
+ *   stats (4 floats, device): min, max, out_depth[0,0,h/2,w/2], radius = min(centre * radius_scale, 5)
+ * The host reads the 16 bytes of `stats` (pose generation stays on the host, DESIGN.md "H2"); the depth map stays in HBM.
+ */
+int tcw_depth_post(tcw_ctx* ctx, const float* res, int n, int h, int w, int c, float near_v, float far_v,
+                   float radius_scale, float* out_depth, float* stats, void* cuda_stream);
+
+/*
+ * Peer-visible device buffers for the multi-GPU exchange (the reference has no collective: every frame is warped on one
+ * device, demo.py:77-90; the build shards units over ranks and assembles colour + mask on the denoiser's rank).
+ * tcw_ipc_alloc: cudaMalloc on ctx's device + cudaIpcGetMemHandle; `handle` receives TCW_IPC_HANDLE_BYTES bytes to send to
+ * the other ranks (any transport).  tcw_ipc_open maps another PROCESS's buffer into this one (peer access over NVLink /
+ * NVSwitch); the returned pointer is valid as out_frame / out_mask of tcw_forward_warp on ctx's device.
+ */
+#define TCW_IPC_HANDLE_BYTES 64
+int tcw_ipc_alloc(tcw_ctx* ctx, size_t bytes, void** ptr, unsigned char* handle);
+int tcw_ipc_free(tcw_ctx* ctx, void* ptr);
+int tcw_ipc_open(tcw_ctx* ctx, const unsigned char* handle, void** ptr);
+int tcw_ipc_close(tcw_ctx* ctx, void* ptr);
 
 #ifdef __cplusplus
 }

@@ -138,3 +138,154 @@ def resize_pack(frame, mask, size):
     rc = lib().orc_resize_pack(_fp(frame), _fp(mask), n, H, W, h, w, _fp(video), _fp(masks))
     assert rc == 0, rc
     return video, masks
+
+
+def depth_post(res, near=0.0001, far=10000.0, radius_scale=1.0):
+    """models/infer.py:79-92 restated in numpy float32, one correctly rounded operation at a time (no torch): channel
+    mean ((a + b) + c) / 3, min / max normalisation over the whole clip, * 3900, floor at 1e-5, 10000 / x, clip; and the
+    radius of demo.py:539-543.  res (n,h,w,c) or (n,h,w).  Returns (depths (n,1,h,w) float32, stats float32[4] = min, max,
+    centre depth, min(centre * radius_scale, 5))."""
+    res = np.asarray(res, dtype=np.float32)
+    if res.ndim == 4:
+        s = res[..., 0].copy()
+        for k in range(1, res.shape[-1]):
+            s = (s + res[..., k]).astype(np.float32)
+        if res.shape[-1] > 1:
+            s = (s / np.float32(res.shape[-1])).astype(np.float32)
+        res = s
+    lo, hi = np.float32(res.min()), np.float32(res.max())
+    d = ((res - lo).astype(np.float32) / np.float32(hi - lo)).astype(np.float32)
+    d = (d * np.float32(3900.0)).astype(np.float32)
+    d = np.where(d < np.float32(1e-5), np.float32(1e-5), d).astype(np.float32)
+    # torch evaluates `10000.0 / tensor` as tensor.reciprocal() * 10000.0: two roundings (probed on torch 2.11 CPU)
+    d = ((np.float32(1.0) / d).astype(np.float32) * np.float32(10000.0)).astype(np.float32)
+    d = np.clip(d, np.float32(near), np.float32(far)).astype(np.float32)[:, None]
+    centre = d[0, 0, d.shape[-2] // 2, d.shape[-1] // 2]
+    radius = np.float32(min(np.float32(centre * np.float32(radius_scale)), np.float32(5.0)))
+    return d, np.array([lo, hi, centre, radius], dtype=np.float32)
+
+
+# ---------------------------------------------------------------------------------------------
+# SURVEY 8f N2: the fork's global point-cloud renderer, restated in numpy
+# (reference notebooks/06_10_25_vggt/warper_point_cloud.py; pinned by tests/golden/pointcloud_cases.npz)
+# ---------------------------------------------------------------------------------------------
+def _fma32(a, b, c):
+    """float32 fused multiply-add through float64 (the product of two float32 is exact in float64)."""
+    return (np.asarray(a, np.float64) * np.asarray(b, np.float64) + np.asarray(c, np.float64)).astype(np.float32)
+
+
+def _gemm_rows(Mrows, cols):
+    """Rows of `M @ X` the way torch's CPU GEMM evaluates them here: per element a chain of fmas from 0 in index order."""
+    out = []
+    for row in Mrows:
+        acc = np.zeros(cols[0].shape, np.float32)
+        for k, c in enumerate(cols):
+            acc = _fma32(np.float32(row[k]), c, acc)
+        out.append(acc)
+    return out
+
+
+def pc_project(points, T, K):
+    """:534-543 / :199-226: camera = T @ [p, 1], projected = K @ camera, pixel = projected.xy / projected.z."""
+    p = np.asarray(points, np.float32)
+    one = np.ones(p.shape[0], np.float32)
+    cam = _gemm_rows(np.asarray(T, np.float32)[:3], [p[:, 0], p[:, 1], p[:, 2], one])
+    proj = _gemm_rows(np.asarray(K, np.float32), cam)
+    with np.errstate(divide="ignore", invalid="ignore"):
+        px = (proj[0] / proj[2]).astype(np.float32)
+        py = (proj[1] / proj[2]).astype(np.float32)
+    return cam, proj, px, py
+
+
+def pc_lift(frame, mask1, depth, T1inv, K1inv, step=1):
+    """lift_to_3d_pointcloud (:12-77): broadcast matmuls = sequential un-fused float32 like models/utils.py:388-399.
+    frame (b,3,h,w), depth (b,1,h,w); T1inv (b,4,4), K1inv (b,3,3) already inverted (torch.linalg.inv on the host)."""
+    frame, depth = _f32(frame), _f32(depth)
+    b, _, h, w = frame.shape
+    ys, xs = np.meshgrid(np.arange(h, dtype=np.float32) * np.float32(step), np.arange(w, dtype=np.float32) * np.float32(step), indexing="ij")
+    m = np.ones((b, h, w), np.float32) if mask1 is None else _f32(mask1)[:, 0]
+    pts = np.empty((b, h, w, 3), np.float32)
+
+    def dot(row, cols):
+        acc = np.zeros(cols[0].shape, np.float32)
+        for k, c in enumerate(cols):
+            acc = (acc + (np.float32(row[k]) * c).astype(np.float32)).astype(np.float32)
+        return acc
+    one = np.ones((h, w), np.float32)
+    for i in range(b):
+        Ki, Ti = np.asarray(K1inv[i], np.float32), np.asarray(T1inv[i], np.float32)
+        u = [dot(Ki[r], [xs, ys, one]) for r in range(3)]
+        X = [(depth[i, 0] * u[r]).astype(np.float32) for r in range(3)]
+        for r in range(3):
+            pts[i, ..., r] = (dot(Ti[r], [X[0], X[1], X[2], one]) * m[i]).astype(np.float32)
+    cols = (np.transpose(frame, (0, 2, 3, 1)) * m[..., None]).astype(np.float32)
+    return pts, cols
+
+
+def pc_zbuffer(points, colors, T, K, h, w, point_size=1, clamp=False):
+    """render_pointcloud_zbuffer_vectorized_point_size (:522-646) / render_pointcloud_zbuffer_vectorized (:445-519, clamp=True).
+    Nearest entry per pixel; among equal depths the LAST entry in (point, offset) order (the sequential CPU index_put).
+    Returns frame (1,3,h,w) with -1 in empty pixels, mask (1,1,h,w), depth (1,1,h,w)."""
+    colors = np.asarray(colors, np.float32)
+    cam, _, px, py = pc_project(points, T, K)
+    z = cam[2]
+    valid = (z > np.float32(0.01)) & (px >= 0) & (px < w) & (py >= 0) & (py < h)
+    idx = np.nonzero(valid)[0]
+    r = 0 if clamp else point_size // 2
+    offs = [(dx, dy) for dy in range(-r, r + 1) for dx in range(-r, r + 1)]
+    frame = np.full((3, h * w), -1.0, np.float32)
+    dbuf = np.zeros(h * w, np.float32)
+    if idx.size:
+        ex = np.stack([np.rint((px[idx] + np.float32(dx)).astype(np.float32)) for dx, _ in offs], 1).astype(np.int64)
+        ey = np.stack([np.rint((py[idx] + np.float32(dy)).astype(np.float32)) for _, dy in offs], 1).astype(np.int64)
+        if clamp:
+            ex, ey = np.clip(ex, 0, w - 1), np.clip(ey, 0, h - 1)
+        ez = np.repeat(z[idx][:, None], len(offs), 1)
+        ep = np.repeat(idx[:, None], len(offs), 1)
+        inb = (ex >= 0) & (ex < w) & (ey >= 0) & (ey < h)
+        lin, ez, ep = (ey * w + ex)[inb], ez[inb], ep[inb]
+        # sort by (pixel, depth, entry order): the first of each pixel's minimum-depth run ends at its last entry
+        order = np.lexsort((np.arange(lin.size), ez, lin))
+        lin, ez, ep = lin[order], ez[order], ep[order]
+        first = np.ones(lin.size, bool)
+        first[1:] = lin[1:] != lin[:-1]
+        start = np.nonzero(first)[0]
+        end = np.append(start[1:], lin.size)
+        for s0, e0 in zip(start, end):
+            k = s0
+            while k + 1 < e0 and ez[k + 1] == ez[s0]:
+                k += 1
+            frame[:, lin[s0]] = colors[ep[k]]
+            dbuf[lin[s0]] = ez[s0]
+    return frame.reshape(1, 3, h, w), (dbuf > 0).astype(np.float32).reshape(1, 1, h, w), dbuf.reshape(1, 1, h, w)
+
+
+def pc_bilinear(points, colors, weights, T, K, h, w, depth_threshold=100000.0):
+    """render_from_camera(use_bilinear=True) for one camera (:199-250) + _splat_points_bilinear_efficient (:351-443).
+    Sequential float32 scatter in the reference's order (NW, NE, SW, SE blocks of all points).  Returns (3,h,w), (1,h,w)."""
+    colors, weights = np.asarray(colors, np.float32), np.asarray(weights, np.float32).reshape(-1)
+    cam, proj, px, py = pc_project(points, T, K)
+    vis = (cam[2] > np.float32(0.1)) & (cam[2] < np.float32(depth_threshold)) & (px >= 0) & (px < w) & (py >= 0) & (py < h)
+    out = np.zeros((3, h * w), np.float32)
+    wb = np.zeros(h * w, np.float32)
+    if vis.any():
+        x, y, d, c, wt = px[vis], py[vis], proj[2][vis], colors[vis], weights[vis]
+        nd = ((d - d.min()).astype(np.float32) / np.float32(np.float32(d.max() - d.min()) + np.float32(1e-8))).astype(np.float32)
+        pw = (wt * np.exp((-nd * np.float32(2)).astype(np.float32)).astype(np.float32)).astype(np.float32)
+        fx0, fy0 = np.floor(x), np.floor(y)
+        dx, dy = (x - fx0).astype(np.float32), (y - fy0).astype(np.float32)
+        ax, ay = (np.float32(1) - dx).astype(np.float32), (np.float32(1) - dy).astype(np.float32)
+        x0, y0 = fx0.astype(np.int64), fy0.astype(np.int64)
+        ws_ = [((ax * ay).astype(np.float32) * pw).astype(np.float32), ((dx * ay).astype(np.float32) * pw).astype(np.float32),
+               ((ax * dy).astype(np.float32) * pw).astype(np.float32), ((dx * dy).astype(np.float32) * pw).astype(np.float32)]
+        for k, wk in enumerate(ws_):
+            xx, yy = x0 + (k & 1), y0 + (k >> 1)
+            ok = (xx >= 0) & (xx < w) & (yy >= 0) & (yy < h) & (wk > np.float32(1e-8))
+            lin = (yy * w + xx)[ok]
+            for ch in range(3):
+                np.add.at(out[ch], lin, (c[ok, ch] * wk[ok]).astype(np.float32))
+            np.add.at(wb, lin, wk[ok])
+        v = wb > np.float32(1e-8)
+        out[:, v] = (out[:, v] / wb[v]).astype(np.float32)
+        return out.reshape(3, h, w), v.astype(np.float32).reshape(1, h, w)
+    return out.reshape(3, h, w), wb.reshape(1, h, w)

@@ -184,3 +184,47 @@ def test_twice_fullsize(warper, clip):
     assert err <= 2e-5
     valid = (gm > 0) & (tm > 0)
     assert (np.abs(gd - td)[valid] <= 2e-5 * np.abs(td[valid])).all()
+
+
+def test_u8_mask_into_exchange_buffer(warper, clip):
+    """The fused exchange writes colour f32 + mask u8 (13 B/px) straight into the destination rank's buffer: here the
+    owner side on one GPU (tcw_ipc_alloc'd memory, slices at a unit offset), against the plain outputs bit for bit."""
+    from trajectorycrafter_b200.sharding import PeerBuffer, packed_buffer, packed_views
+    frames, depths = clip
+    T1, T2, K, src = orbit_units(depths[:4], H, W, presets=ORBIT_PRESETS[:2])
+    M = prepare_matrices(T1, T2, K)
+    plain = warper.forward_warp_matrices(frames[:4], depths[:4], M, src_index=src)
+    buf = PeerBuffer(warper, 12, H, W, dst=0)
+    try:
+        col, msk = buf.views(3, 11)
+        got = warper.forward_warp_matrices(frames[:4], depths[:4], M, src_index=src, out=(col, msk, None, None), mask_u8=True)
+        torch.cuda.synchronize()
+        assert got[1].dtype == torch.uint8
+        assert torch.equal(buf.colour[3:11], plain[0]) and torch.equal(buf.mask[3:11].float(), plain[1])
+    finally:
+        buf.close()
+    packed = packed_buffer(8, H, W, warper.device)
+    pc, pm = packed_views(packed, 8, H, W)
+    warper.forward_warp_matrices(frames[:4], depths[:4], M, src_index=src, out=(pc, pm, None, None), mask_u8=True)
+    assert torch.equal(pc, plain[0]) and torch.equal(pm.float(), plain[1])
+
+
+@pytest.mark.parametrize("name", ["small", "clip", "odd", "video"])
+def test_depth_postprocess_on_device(warper, name):
+    """SURVEY 8f N4: tcw_depth_post against the reference's own lines (models/infer.py:79-92, demo.py:539-543) bit for bit;
+    the radius reaches the pose generator through 16 pinned bytes and an event, the depth map never leaves the device."""
+    import os
+    from trajectorycrafter_b200.poses import get_poses
+    z = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "depth_cases.npz"))
+    near, far, scale = [float(v) for v in z[name + "/params"]]
+    depths, stats = warper.depth_postprocess(torch.from_numpy(z[name + "/res"]), near, far, scale)
+    stats.ready.synchronize()                      # 16 bytes, not the stream
+    assert depths.is_cuda and bit_equal(npy(depths), z[name + "/depths"])
+    assert float(stats[3]) == float(z[name + "/radius"])
+    od, ost = oracle.depth_post(z[name + "/res"], near, far, scale)
+    assert np.array_equal(stats.numpy(), ost)
+    n = depths.shape[0]
+    a = get_poses(depths.cpu(), n, target_pose=(0, 30, 0.3, 0, 0), radius_scale=scale)
+    b = get_poses(None, n, target_pose=(0, 30, 0.3, 0, 0), radius_scale=scale, centre_depth=float(stats[2]))
+    for x, y in zip(a, b):
+        assert torch.equal(x, y), "poses from the device-side centre depth differ from the read-back path"

@@ -56,3 +56,45 @@ def test_gather_even_shards():
 
 def test_gather_ragged_shards():
     _run(7)
+
+
+def _worker_packed(rank, world, port, n_units, results):
+    from trajectorycrafter_b200.sharding import gather_packed, packed_buffer, packed_views, unpack_gathered
+    os.environ["MASTER_ADDR"] = "127.0.0.1"
+    os.environ["MASTER_PORT"] = str(port)
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        h, w = 6, 10
+        g = torch.Generator().manual_seed(5)
+        colour_all = torch.rand((n_units, 3, h, w), generator=g) * 2 - 1
+        mask_all = (torch.rand((n_units, 1, h, w), generator=g) > 0.4).to(torch.uint8)
+        lo, hi = shard_bounds(n_units, world, rank)
+        packed = packed_buffer(hi - lo, h, w, "cpu")
+        col, msk = packed_views(packed, hi - lo, h, w)
+        col.copy_(colour_all[lo:hi])            # on the GPU the warp writes these views itself (out=, mask_u8=True)
+        msk.copy_(mask_all[lo:hi])
+        got = gather_packed(packed, n_units, h, w, dst=0)
+        if rank == 0:
+            parts = unpack_gathered(got, n_units, h, w)
+            ok = torch.equal(torch.cat([p[0] for p in parts]), colour_all) and torch.equal(torch.cat([p[1] for p in parts]), mask_all)
+            results.put(("ok" if ok else "mismatch", (n_units,)))
+        else:
+            assert got is None
+        dist.barrier()
+    finally:
+        dist.destroy_process_group()
+
+
+def test_single_gather_of_packed_colour_and_u8_mask():
+    """The collective form of the exchange is ONE gather of 13 B per pixel (colour float32 + mask uint8 in one buffer)."""
+    ctx = mp.get_context("spawn")
+    q = ctx.SimpleQueue()
+    port = _free_port()
+    procs = [ctx.Process(target=_worker_packed, args=(r, 2, port, 8, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    for p in procs:
+        p.join(120)
+        assert p.exitcode == 0
+    status, shape = q.get()
+    assert status == "ok"

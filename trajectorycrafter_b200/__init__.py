@@ -9,6 +9,7 @@ from .poses import (generate_traj_specified, generate_traj_txt, get_poses, spher
                     txt_interpolation)
 from .matrices import prepare_matrices  # noqa: F401
 from .warper import Warper  # noqa: F401
+from .pointcloud import GlobalPointCloudWarper  # noqa: F401
 
-__all__ = ["Warper", "prepare_matrices", "sphere2pose", "generate_traj_specified",
+__all__ = ["Warper", "GlobalPointCloudWarper", "prepare_matrices", "sphere2pose", "generate_traj_specified",
            "generate_traj_txt", "txt_interpolation", "get_poses"]

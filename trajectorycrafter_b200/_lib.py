@@ -15,6 +15,8 @@ TCW_CLEAN = 4
 TCW_IS_IMAGE = 8
 TCW_ATOMIC_F32 = 16
 TCW_HOST_MASK_U8 = 32
+TCW_MASK_U8 = 64
+TCW_IPC_HANDLE_BYTES = 64
 # status bits a call ORs into its range_flag word
 TCW_STATUS_RANGE = 1
 TCW_STATUS_UNORDERED = 2
@@ -41,6 +43,14 @@ SIGNATURES = {
                           _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
     "tcw_clean_points": (c_int, [c_void_p, _FP, _FP, c_int, c_int, c_int, _VP, _VP, c_void_p]),
     "tcw_resize_pack": (c_int, [c_void_p, _FP, _FP, c_int, c_int, c_int, c_int, c_int, _FP, _FP, c_void_p]),
+    "tcw_pc_lift": (c_int, [c_void_p, _FP, _FP, _FP, _FP, c_int, c_int, c_int, c_int, _FP, _FP, c_void_p]),
+    "tcw_pc_render_zbuffer": (c_int, [c_void_p, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_int, _FP, _FP, _FP, _VP, c_size_t, c_void_p]),
+    "tcw_pc_render_bilinear": (c_int, [c_void_p, _FP, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_float, _FP, _FP, _VP, c_size_t, c_void_p]),
+    "tcw_depth_post": (c_int, [c_void_p, _FP, c_int, c_int, c_int, c_int, c_float, c_float, c_float, _FP, _FP, c_void_p]),
+    "tcw_ipc_alloc": (c_int, [c_void_p, c_size_t, POINTER(c_void_p), c_void_p]),
+    "tcw_ipc_free": (c_int, [c_void_p, c_void_p]),
+    "tcw_ipc_open": (c_int, [c_void_p, c_void_p, POINTER(c_void_p)]),
+    "tcw_ipc_close": (c_int, [c_void_p, c_void_p]),
 }
 
 _lib = None

@@ -253,6 +253,8 @@ __device__ __forceinline__ float block_max_256(float v) {
 #include "warp_pair.cuh"
 #include "warp_window.cuh"
 #include "resize_pack.cuh"
+#include "depth_post.cuh"
+#include "pointcloud.cuh"
 
 // ----------------------------------------------------------------------------------------------
 // compute_transformed_points as a standalone op
@@ -491,6 +493,7 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
         LAUNCH_CHECK("k_splat_window");
         WinNormArgs N;
         N.out_c = J.out_c; N.is_image = J.is_image; N.range_flag = J.range_flag; N.out_depth = J.out_depth;
+        N.mask_u8 = (J.flags & TCW_MASK_U8) ? 1 : 0;
         if (clean) {
             // fp32 results of the chunk go to scratch (laid out as units u0.. of a (n,3,h,w) / (n,1,h,w) pair), clean_points makes them float64
             N.out_frame = tmp + (size_t)slot0 * 4 * hw - (size_t)u0 * J.out_c * hw;
@@ -684,6 +687,8 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
     if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp: src_index is NULL but n_src != n_units");
     if ((flags & TCW_DETERMINISTIC) && (flags & TCW_ATOMIC_F32)) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_DETERMINISTIC and TCW_ATOMIC_F32 exclude each other");
     if ((flags & TCW_ATOMIC_F32) && (flags & TCW_CLEAN)) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_ATOMIC_F32 has no fused clean_points");
+    if ((flags & TCW_MASK_U8) && (flags & (TCW_CLEAN | TCW_ATOMIC_F32 | TCW_DETERMINISTIC)))
+        return fail(TCW_E_ARG, "tcw_forward_warp: TCW_MASK_U8 needs the default mode without TCW_CLEAN");
     const size_t hw = (size_t)h * w;
     if (hw >= 0x7fffffffull / 4) return fail(TCW_E_ARG, "tcw_forward_warp: image too large for this build");
     cudaStream_t st = (cudaStream_t)cuda_stream;
@@ -829,6 +834,146 @@ TCW_API int tcw_resize_pack(tcw_ctx* ctx, const float* frame, const float* mask,
     k_resize_pack<<<blocks, 256, 0, (cudaStream_t)cuda_stream>>>(frame, mask, n, H, W, h, w, (float)H / (float)h, (float)W / (float)w,
                                                                out_video, out_masks);
     LAUNCH_CHECK("k_resize_pack");
+    return TCW_OK;
+}
+
+// ----------------------------------------------------------------------------------------------
+// global point-cloud renderer (reference notebooks/06_10_25_vggt/warper_point_cloud.py)
+// ----------------------------------------------------------------------------------------------
+TCW_API int tcw_pc_lift(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth, const float* Minv,
+                        int b, int h, int w, int step, float* out_points, float* out_colors, void* cuda_stream) {
+    if (!ctx || !frame || !depth || !Minv || !out_points || !out_colors) return fail(TCW_E_ARG, "tcw_pc_lift: NULL argument");
+    if (b <= 0 || b > 65535 || h <= 0 || w <= 0 || step < 1) return fail(TCW_E_ARG, "tcw_pc_lift: bad shape");
+    const size_t hw = (size_t)h * w;
+    k_pc_lift<<<dim3((unsigned)((hw + 255) / 256), b), 256, 0, (cudaStream_t)cuda_stream>>>(frame, mask1, depth, Minv, h, w, step, out_points, out_colors);
+    LAUNCH_CHECK("k_pc_lift");
+    return TCW_OK;
+}
+
+static int pc_grid(const tcw_ctx* ctx, long long n) {
+    const long long want = (n + 255) / 256, cap = (long long)ctx->sm_count * 8;
+    return (int)(want < cap ? (want > 0 ? want : 1) : cap);
+}
+
+TCW_API int tcw_pc_render_zbuffer(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                                  long long n_points, int h, int w, int point_size,
+                                  float* out_frame, float* out_mask, float* out_depth,
+                                  void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    if (!ctx || !camera || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer: NULL argument");
+    if (n_points < 0 || (n_points > 0 && (!points || !colors)) || h <= 0 || w <= 0 || point_size < 0 || point_size > 64)
+        return fail(TCW_E_ARG, "tcw_pc_render_zbuffer: bad argument");
+    const int radius = point_size / 2, n_splats = (2 * radius + 1) * (2 * radius + 1);
+    if (n_points * (long long)n_splats >= 0xffffffffll) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer: too many footprint entries (< 2^32)");
+    const size_t hw = (size_t)h * w;
+    if (hw >= 0x7fffffffull) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer: image too large");
+    if (!workspace || workspace_bytes < hw * sizeof(unsigned long long)) return fail(TCW_E_WORKSPACE, "tcw_pc_render_zbuffer: workspace needs h*w*8 bytes");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    PcCamera C;
+    memcpy(C.T, camera, sizeof(C.T));
+    memcpy(C.K, camera + 12, sizeof(C.K));
+    unsigned long long* zbuf = (unsigned long long*)workspace;
+    CUDA_TRY(cudaMemsetAsync(zbuf, 0xff, hw * sizeof(unsigned long long), st));
+    if (n_points > 0) {
+        k_pc_zbuffer<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, C, n_points, h, w, point_size, zbuf);
+        LAUNCH_CHECK("k_pc_zbuffer");
+    }
+    k_pc_resolve<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(zbuf, colors, (int)hw, n_splats, out_frame, out_mask, out_depth);
+    LAUNCH_CHECK("k_pc_resolve");
+    return TCW_OK;
+}
+
+TCW_API int tcw_pc_render_bilinear(tcw_ctx* ctx, const float* points, const float* colors, const float* weights, const float* camera,
+                                   long long n_points, int h, int w, float depth_threshold,
+                                   float* out_frame, float* out_mask, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    if (!ctx || !camera || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_pc_render_bilinear: NULL argument");
+    if (n_points < 0 || (n_points > 0 && (!points || !colors || !weights)) || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_pc_render_bilinear: bad argument");
+    const size_t hw = (size_t)h * w;
+    if (hw >= 0x7fffffffull) return fail(TCW_E_ARG, "tcw_pc_render_bilinear: image too large");
+    if (!workspace || workspace_bytes < 256 + hw * sizeof(float4)) return fail(TCW_E_WORKSPACE, "tcw_pc_render_bilinear: workspace needs 256 + h*w*16 bytes");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    PcCamera C;
+    memcpy(C.T, camera, sizeof(C.T));
+    memcpy(C.K, camera + 12, sizeof(C.K));
+    unsigned* mm = (unsigned*)workspace;
+    float4* acc = (float4*)((char*)workspace + 256);
+    CUDA_TRY(cudaMemsetAsync(mm, 0xff, sizeof(unsigned), st));
+    CUDA_TRY(cudaMemsetAsync(mm + 1, 0, 2 * sizeof(unsigned), st));
+    CUDA_TRY(cudaMemsetAsync(acc, 0, hw * sizeof(float4), st));
+    if (n_points > 0) {
+        k_pc_range<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, C, n_points, h, w, depth_threshold, mm);
+        LAUNCH_CHECK("k_pc_range");
+        k_pc_bilinear<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, colors, weights, C, n_points, h, w, depth_threshold, mm, acc);
+        LAUNCH_CHECK("k_pc_bilinear");
+    }
+    k_pc_normalise<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(acc, (int)hw, out_frame, out_mask);
+    LAUNCH_CHECK("k_pc_normalise");
+    return TCW_OK;
+}
+
+// depth post-processing + trajectory radius on the device (models/infer.py:79-92, demo.py:539-543)
+TCW_API int tcw_depth_post(tcw_ctx* ctx, const float* res, int n, int h, int w, int c, float near_v, float far_v,
+                           float radius_scale, float* out_depth, float* stats, void* cuda_stream) {
+    if (!ctx || !res || !out_depth || !stats) return fail(TCW_E_ARG, "tcw_depth_post: NULL argument");
+    if (n <= 0 || h <= 0 || w <= 0 || c < 1 || c > 4) return fail(TCW_E_ARG, "tcw_depth_post: bad shape");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    const size_t n_px = (size_t)n * h * w;
+    unsigned* mm = (unsigned*)stats;
+    CUDA_TRY(cudaMemsetAsync(mm, 0xff, sizeof(unsigned), st));          // running minimum starts at the largest code
+    CUDA_TRY(cudaMemsetAsync(mm + 1, 0, sizeof(unsigned), st));
+    const size_t want = (n_px + 255) / 256;
+    const int blocks = (int)(want < (size_t)ctx->sm_count * 8 ? want : (size_t)ctx->sm_count * 8);
+    k_depth_minmax<<<blocks, 256, 0, st>>>(res, n_px, c, mm);
+    LAUNCH_CHECK("k_depth_minmax");
+    k_depth_post<<<blocks, 256, 0, st>>>(res, n_px, c, mm, near_v, far_v, out_depth);
+    LAUNCH_CHECK("k_depth_post");
+    k_depth_stats<<<1, 32, 0, st>>>(mm, out_depth, h, w, radius_scale);
+    LAUNCH_CHECK("k_depth_stats");
+    return TCW_OK;
+}
+
+// ----------------------------------------------------------------------------------------------
+// peer-visible buffers (multi-GPU exchange)
+// ----------------------------------------------------------------------------------------------
+struct DevGuard {
+    int prev; bool ok;
+    explicit DevGuard(int dev) : prev(0), ok(false) { ok = cudaGetDevice(&prev) == cudaSuccess && cudaSetDevice(dev) == cudaSuccess; }
+    ~DevGuard() { cudaSetDevice(prev); }
+};
+
+TCW_API int tcw_ipc_alloc(tcw_ctx* ctx, size_t bytes, void** ptr, unsigned char* handle) {
+    if (!ctx || !ptr || !handle || bytes == 0) return fail(TCW_E_ARG, "tcw_ipc_alloc: bad argument");
+    static_assert(sizeof(cudaIpcMemHandle_t) == TCW_IPC_HANDLE_BYTES, "IPC handle size");
+    DevGuard g(ctx->device);
+    if (!g.ok) return fail(TCW_E_CUDA, "tcw_ipc_alloc: cannot select the device");
+    void* p = nullptr;
+    cudaError_t e = cudaMalloc(&p, bytes);
+    if (e != cudaSuccess) return fail(TCW_E_NOMEM, "tcw_ipc_alloc: cudaMalloc failed: %s", cudaGetErrorString(e));
+    cudaIpcMemHandle_t hnd;
+    e = cudaIpcGetMemHandle(&hnd, p);
+    if (e != cudaSuccess) { cudaFree(p); return fail(TCW_E_CUDA, "tcw_ipc_alloc: cudaIpcGetMemHandle failed: %s", cudaGetErrorString(e)); }
+    memcpy(handle, &hnd, sizeof(hnd));
+    *ptr = p;
+    return TCW_OK;
+}
+TCW_API int tcw_ipc_free(tcw_ctx* ctx, void* ptr) {
+    if (!ctx || !ptr) return fail(TCW_E_ARG, "tcw_ipc_free: bad argument");
+    DevGuard g(ctx->device);
+    CUDA_TRY(cudaFree(ptr));
+    return TCW_OK;
+}
+TCW_API int tcw_ipc_open(tcw_ctx* ctx, const unsigned char* handle, void** ptr) {
+    if (!ctx || !handle || !ptr) return fail(TCW_E_ARG, "tcw_ipc_open: bad argument");
+    DevGuard g(ctx->device);
+    if (!g.ok) return fail(TCW_E_CUDA, "tcw_ipc_open: cannot select the device");
+    cudaIpcMemHandle_t hnd;
+    memcpy(&hnd, handle, sizeof(hnd));
+    CUDA_TRY(cudaIpcOpenMemHandle(ptr, hnd, cudaIpcMemLazyEnablePeerAccess));
+    return TCW_OK;
+}
+TCW_API int tcw_ipc_close(tcw_ctx* ctx, void* ptr) {
+    if (!ctx || !ptr) return fail(TCW_E_ARG, "tcw_ipc_close: bad argument");
+    DevGuard g(ctx->device);
+    CUDA_TRY(cudaIpcCloseMemHandle(ptr));
     return TCW_OK;
 }
 

@@ -123,14 +123,26 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
         // float2 accesses when both pixels exist in every lane that has any, rows stay 8-byte aligned
         const bool vec2 = __all_sync(FULL, okB || !okA) && !(w & 1) &&
             !((((size_t)dp) | ((size_t)flp) | ((size_t)zp) | ((size_t)gfl)) & 7);
-        for (int y = y0; y < y1; ++y) {
+        // the strip's depth values up front: eight independent loads in flight instead of one per row
+        float2 dpre[8];
+        if (PROJECT) {
+            #pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                const int y = y0 + r < y1 ? y0 + r : y1 - 1;
+                const size_t qA = (size_t)y * w + cA, qB = (size_t)y * w + cB;
+                if (vec2) dpre[r] = __ldg((const float2*)(dp + qA));
+                else dpre[r] = make_float2(__ldg(dp + qA), __ldg(dp + qB));
+            }
+        }
+        #pragma unroll
+        for (int r = 0; r < 8; ++r) {
+            const int y = y0 + r;
+            if (y >= y1) break;
             const float fy = (float)y;
             const size_t qA = (size_t)y * w + cA, qB = (size_t)y * w + cB;
             float flxA, flxB, flyA, flyB, zA, zB;
             if (PROJECT) {
-                float dA, dB;
-                if (vec2) { const float2 t = __ldg((const float2*)(dp + qA)); dA = t.x; dB = t.y; }
-                else { dA = __ldg(dp + qA); dB = __ldg(dp + qB); }
+                const float dA = dpre[r].x, dB = dpre[r].y;
                 float P0A, P1A, P2A, P0B, P1B, P2B, Y2A, Y2B;
                 if (PIN) {
                     const float u1 = __fadd_rn(__fmul_rn(m[4], fy), m[5]);
@@ -887,6 +899,7 @@ struct WinNormArgs {
     float* out_frame; int out_c;          // (n, out_c, h, w): channels 0 .. out_c-1 of the sums / sum w
     float* out_mask; float* out_depth;    // out_depth: fourth sum / sum w (fused path), may be nullptr
     int is_image; int* range_flag;
+    int mask_u8;                          // out_mask is a uint8 buffer (TCW_MASK_U8)
 };
 
 __global__ void __launch_bounds__(128)
@@ -1020,6 +1033,7 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
         const size_t p0 = (size_t)row0 * w + tx;
         float* o0 = N.out_frame + (size_t)u * N.out_c * hw + p0;
         float* om = N.out_mask + (size_t)u * hw + p0;
+        unsigned char* om8 = (unsigned char*)N.out_mask + (size_t)u * hw + p0;
         float* od = N.out_depth ? N.out_depth + (size_t)u * hw + p0 : nullptr;
         const float hole = N.is_image ? -1.0f : 0.0f;
         #pragma unroll
@@ -1038,9 +1052,10 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
                     __stcs(o0 + (size_t)c * hw, x);
                 }
             }
-            __stcs(om, valid ? 1.0f : 0.0f);
+            if (N.mask_u8) *om8 = valid ? 1 : 0;
+            else __stcs(om, valid ? 1.0f : 0.0f);
             if (od) { __stcs(od, valid ? v[3] : 0.0f); od += w; }
-            o0 += w; om += w;
+            o0 += w; om += w; om8 += w;
         }
     }
     if (bad && N.range_flag) atomicOr(N.range_flag, 1);

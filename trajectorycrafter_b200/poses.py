@@ -98,13 +98,20 @@ def get_poses(depths: torch.Tensor, num_frames: int, *, camera: str = "target",
               target_pose: Sequence[float] = (0, 0, 0, 0, 0), traj_txt: Optional[str] = None,
               radius_scale: float = 1.0, anchor_idx: int = 0, device="cpu",
               focal: float = 500.0, cx: float = 512.0, cy: float = 288.0,
-              f_new: Optional[float] = None):
+              f_new: Optional[float] = None, centre_depth=None):
     """demo.py:538-586 (and :588-632 when ``f_new`` is given: focal ramps linearly to f_new).
 
-    Returns (pose_s (n,4,4), pose_t (n,4,4), K (n,3,3)).  radius = min(centre depth of frame 0 *
+    ``centre_depth``: skip the read-back of the centre depth pixel and use this value (``stats[2]`` of
+    ``Warper.depth_postprocess``).  Returns (pose_s (n,4,4), pose_t (n,4,4), K (n,3,3)).  radius = min(centre depth of frame 0 *
     radius_scale, 5); every pose is pushed back by +radius along z; pose_s repeats the anchor pose.
     """
-    radius = depths[0, 0, depths.shape[-2] // 2, depths.shape[-1] // 2].cpu() * radius_scale
+    if centre_depth is None:
+        centre = depths[0, 0, depths.shape[-2] // 2, depths.shape[-1] // 2].cpu()
+    else:
+        # the centre pixel already fetched by Warper.depth_postprocess (stats[2]): the depth map is not read back; a
+        # float32 0-d tensor like the reference's own value, so the two lines below are the reference's arithmetic
+        centre = torch.tensor(float(centre_depth), dtype=torch.float32)
+    radius = centre * radius_scale
     radius = min(radius, 5)
     if f_new is None:
         K = torch.tensor([[focal, 0.0, cx], [0.0, focal, cy], [0.0, 0.0, 1.0]]).repeat(num_frames, 1, 1).to(device)

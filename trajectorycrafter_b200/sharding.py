@@ -70,3 +70,88 @@ def gather_condition_video(colour: torch.Tensor, mask: torch.Tensor, n_units: in
         keep = torch.cat([torch.arange(r * cmax, r * cmax + c) for r, c in enumerate(counts)]).to(col_all.device)
         col_all, msk_all = col_all[keep], msk_all[keep]
     return col_all, msk_all.to(colour.dtype)
+
+
+# ---------------------------------------------------------------------------------------------
+# The fused form of the exchange: no collective at all.  The destination rank owns one buffer laid out as
+# [colour (n,3,h,w) float32 | mask (n,1,h,w) uint8] = 13 B per pixel; every other rank maps it (CUDA IPC over
+# NVLink / NVSwitch) and its gather kernel stores its units' colour and mask straight into its slice.
+# ---------------------------------------------------------------------------------------------
+class _DevicePointer:
+    """Raw device memory as a __cuda_array_interface__ object (torch.as_tensor wraps it without a copy)."""
+
+    def __init__(self, ptr: int, shape, typestr: str):
+        self.__cuda_array_interface__ = {"shape": tuple(shape), "typestr": typestr, "data": (int(ptr), False), "version": 3,
+                                         "strides": None}
+
+
+class PeerBuffer:
+    """The condition video of one clip on the denoiser's rank, writable by every rank.
+
+    ``PeerBuffer(warper, n_units, h, w, dst, group)`` is collective: rank `dst` allocates (``tcw_ipc_alloc``), the 64-byte
+    handle travels once through ``dist.broadcast_object_list`` and the other ranks map it (``tcw_ipc_open``).
+    ``views(lo, hi)`` returns (colour (hi-lo,3,h,w) float32, mask (hi-lo,1,h,w) uint8) tensors over units [lo, hi) of the
+    buffer -- local memory on `dst`, peer memory elsewhere -- to be passed as ``out=`` to ``forward_warp_matrices(...,
+    mask_u8=True)``.  After a barrier ``colour`` / ``mask`` on `dst` hold the assembled clip (what demo.py:117-148 feeds to
+    the pipeline, before its resize)."""
+
+    def __init__(self, warper, n_units: int, h: int, w: int, dst: int = 0, group: Optional[dist.ProcessGroup] = None):
+        import ctypes
+        from . import _lib
+        self.warper, self.n, self.h, self.w, self.dst, self.group = warper, n_units, h, w, dst, group
+        self.rank = dist.get_rank(group) if dist.is_initialized() else 0
+        self.owner = self.rank == dst
+        lib, ctx = warper._lib, warper._context()
+        self.colour_bytes = n_units * 3 * h * w * 4
+        total = self.colour_bytes + n_units * h * w
+        handle = (ctypes.c_ubyte * _lib.TCW_IPC_HANDLE_BYTES)()
+        ptr = ctypes.c_void_p()
+        if self.owner:
+            _lib.check(lib.tcw_ipc_alloc(ctx, total, ctypes.byref(ptr), handle), "tcw_ipc_alloc")
+        box = [bytes(handle) if self.owner else None]
+        if dist.is_initialized() and dist.get_world_size(group) > 1:
+            dist.broadcast_object_list(box, src=dst, group=group)
+        if not self.owner:
+            buf = (ctypes.c_ubyte * _lib.TCW_IPC_HANDLE_BYTES).from_buffer_copy(box[0])
+            _lib.check(lib.tcw_ipc_open(ctx, buf, ctypes.byref(ptr)), "tcw_ipc_open")
+        self.ptr = int(ptr.value)
+        dev = warper.device
+        self.colour = torch.as_tensor(_DevicePointer(self.ptr, (n_units, 3, h, w), "<f4"), device=dev)
+        self.mask = torch.as_tensor(_DevicePointer(self.ptr + self.colour_bytes, (n_units, 1, h, w), "|u1"), device=dev)
+
+    def views(self, lo: int, hi: int):
+        return self.colour[lo:hi], self.mask[lo:hi]
+
+    def close(self):
+        if self.ptr:
+            lib, ctx = self.warper._lib, self.warper._context()
+            self.colour = self.mask = None
+            (lib.tcw_ipc_free if self.owner else lib.tcw_ipc_close)(ctx, self.ptr)
+            self.ptr = 0
+
+
+def gather_packed(packed: torch.Tensor, n_units: int, h: int, w: int, dst: int = 0, group: Optional[dist.ProcessGroup] = None):
+    """The collective form with ONE gather: every rank's units as one uint8 buffer [colour float32 | mask uint8]
+    (13 B per pixel, written by the warp itself through ``packed_views``), equal shards.  Returns the (world, bytes) uint8
+    tensor on `dst` (None elsewhere); ``unpack_gathered`` gives the views."""
+    world, rank = dist.get_world_size(group), dist.get_rank(group)
+    assert n_units % world == 0, "gather_packed needs equal shards (pad the unit list)"
+    out = packed.new_empty((world, packed.numel())) if rank == dst else None
+    dist.gather(packed, list(out.unbind(0)) if rank == dst else None, dst=dst, group=group)
+    return out
+
+
+def packed_buffer(n_local: int, h: int, w: int, device) -> torch.Tensor:
+    return torch.empty(n_local * h * w * 13, dtype=torch.uint8, device=device)
+
+
+def packed_views(packed: torch.Tensor, n_local: int, h: int, w: int):
+    """(colour (n,3,h,w) float32, mask (n,1,h,w) uint8) views of one rank's packed buffer."""
+    cb = n_local * 3 * h * w * 4
+    return packed[:cb].view(torch.float32).view(n_local, 3, h, w), packed[cb:].view(n_local, 1, h, w)
+
+
+def unpack_gathered(gathered: torch.Tensor, n_units: int, h: int, w: int):
+    """Per-rank (colour, mask) views of the gathered (world, bytes) buffer, in unit order."""
+    world = gathered.shape[0]
+    return [packed_views(gathered[r], n_units // world, h, w) for r in range(world)]

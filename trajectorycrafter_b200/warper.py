@@ -124,13 +124,14 @@ class Warper:
                               mask1: Optional[torch.Tensor] = None, src_index: Optional[torch.Tensor] = None,
                               per_frame_max: bool = True, mask: bool = False,
                               return_depth: bool = True, return_flow: bool = True, check_range=True,
-                              accumulation: str = "window", out=None):
+                              accumulation: str = "window", out=None, mask_u8: bool = False):
         """``forward_warp_batch`` on an already prepared (n_units,30) matrix block
         (``prepare_matrices``): [K1^-1 | rows 0..2 of T2*T1^-1 | K2] per unit.
 
         ``check_range`` True: raise AssertionError like the reference if a colour left [-1.1,1.1]
         (one host sync); False: skip; an int32 CUDA tensor: OR the flag into it, no sync (check it
-        later).  ``out`` may carry preallocated (frame, mask, depth|None, flow|None) CUDA tensors."""
+        later).  ``out`` may carry preallocated (frame, mask, depth|None, flow|None) CUDA tensors -- they may live in a peer
+        GPU's memory (``sharding.PeerBuffer``).  ``mask_u8``: the validity mask is written as uint8 (default mode only)."""
         n_src, c, h, w = frames.shape
         n = M.shape[0]
         assert c == 3 and depths.shape == (n_src, 1, h, w) and M.shape == (n, 30)
@@ -150,17 +151,20 @@ class Warper:
         M_d = M.to(self.device, torch.float32, non_blocking=True).contiguous()
         si_d = None if src_index is None else src_index.to(self.device, torch.int32).contiguous()
         mode = {"window": 0, "integer": _lib.TCW_DETERMINISTIC, "atomic": _lib.TCW_ATOMIC_F32}[accumulation]
-        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) | mode
+        flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) | mode \
+            | (_lib.TCW_MASK_U8 if mask_u8 else 0)
         odt = torch.float64 if mask else torch.float32
+        mdt = torch.uint8 if mask_u8 else odt
+        assert not (mask_u8 and (mask or mode)), "mask_u8 needs the default accumulation and mask=False"
         if out is not None:
             out_frame, out_mask, out_depth, out_flow = out
             assert out_frame.shape == (n, 3, h, w) and out_frame.dtype == odt and out_frame.is_contiguous()
-            assert out_mask.shape == (n, 1, h, w) and out_mask.dtype == odt and out_mask.is_contiguous()
+            assert out_mask.shape == (n, 1, h, w) and out_mask.dtype == mdt and out_mask.is_contiguous()
             assert out_depth is None or (out_depth.shape == (n, 1, h, w) and out_depth.is_contiguous())
             assert out_flow is None or (out_flow.shape == (n, 2, h, w) and out_flow.is_contiguous())
         else:
             out_frame = torch.empty((n, 3, h, w), dtype=odt, device=self.device)
-            out_mask = torch.empty((n, 1, h, w), dtype=odt, device=self.device)
+            out_mask = torch.empty((n, 1, h, w), dtype=mdt, device=self.device)
             out_depth = torch.empty((n, 1, h, w), dtype=torch.float32, device=self.device) if return_depth else None
             out_flow = torch.empty((n, 2, h, w), dtype=torch.float32, device=self.device) if return_flow else None
         lazy_flag = isinstance(check_range, torch.Tensor)
@@ -380,6 +384,34 @@ class Warper:
                                            _ptr(video), _ptr(cmask), self._stream())
         _lib.check(rc, "tcw_resize_pack")
         return video, cmask
+
+    def depth_postprocess(self, res, near: float = 0.0001, far: float = 10000.0, radius_scale: float = 1.0):
+        """The lines that end the reference's depth stage (models/infer.py:79-92) plus the trajectory radius of
+        demo.py:539-543, on the device: channel mean, min / max normalisation over the whole clip, ``* 3900``, floor at 1e-5,
+        ``10000 / x``, clip -- bit-identical to the numpy / torch lines.
+
+        res (n,h,w,3) (the pipeline's channels-last output) or (n,h,w) float32, on the host or the device.
+        Returns (depths (n,1,h,w) CUDA float32, stats): ``stats`` is a 4-float PINNED host tensor (min, max, centre depth,
+        radius) filled by an asynchronous copy, and ``stats.ready`` the CUDA event behind it -- ``stats.ready.synchronize()``
+        waits for these 16 bytes only, never for the stream (the warp of an earlier clip keeps running).  Pass
+        ``centre_depth=float(stats[2])`` to ``poses.get_poses`` instead of letting it read the depth map back (``stats[3]`` is
+        the radius itself for callers that build poses elsewhere)."""
+        if res.dim() == 3:
+            res = res.unsqueeze(-1)
+        n, h, w, c = res.shape
+        res_d = self._dev(res.contiguous())
+        depths = torch.empty((n, 1, h, w), dtype=torch.float32, device=self.device)
+        stats_d = torch.empty(4, dtype=torch.float32, device=self.device)
+        stats = torch.empty(4, dtype=torch.float32).pin_memory()
+        with torch.cuda.device(self.device):
+            rc = self._lib.tcw_depth_post(self._context(), _ptr(res_d), n, h, w, c, float(near), float(far), float(radius_scale),
+                                          _ptr(depths), _ptr(stats_d), self._stream())
+            _lib.check(rc, "tcw_depth_post")
+            stats.copy_(stats_d, non_blocking=True)
+            ev = torch.cuda.Event()
+            ev.record()
+        stats.ready = ev
+        return depths, stats
 
     @staticmethod
     def create_grid(b, h, w):
