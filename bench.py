@@ -458,6 +458,18 @@ def run_ours(args):
                "d2h_bytes_per_step": int(sum(t.numel() * 4 for t in houts) + 4),
                "ms_per_step": dt * 1e3, "steps": k_e2e,
                "api": "Warper.forward_warp_host -> tcw_forward_warp_host (pinned host buffers)"}
+        # what every shipped caller keeps of the four outputs (`warped, mask, _, _`): colour + mask, the mask as uint8
+        if rank == 0 and world == 1:
+            hc = (houts[0], torch.empty((n_units, 1, H, W), dtype=torch.uint8).pin_memory(), None, None)
+            warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=hc, return_depth=False, return_flow=False, mask_u8=True)
+            t0 = time.perf_counter()
+            for _ in range(k_e2e):
+                warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=hc, return_depth=False, return_flow=False, mask_u8=True)
+            dtc = (time.perf_counter() - t0) / k_e2e
+            e2e["condition_only"] = {"value": px_per_step / dtc / 1e6, "ms_per_step": dtc * 1e3,
+                                     "d2h_bytes_per_step": int(n_units * H * W * 13 + 4),
+                                     "what": "colour f32 + mask u8 only (depth and flow12 stay on the device)"}
+            del hc
         del houts
 
     # ---- multi-GPU as the path is specified: ONE clip's 392 units sharded over the ranks (strong scaling), then the same

@@ -228,3 +228,21 @@ def test_depth_postprocess_on_device(warper, name):
     b = get_poses(None, n, target_pose=(0, 30, 0.3, 0, 0), radius_scale=scale, centre_depth=float(stats[2]))
     for x, y in zip(a, b):
         assert torch.equal(x, y), "poses from the device-side centre depth differ from the read-back path"
+
+
+def test_src_index_is_checked_on_the_device(warper, clip):
+    """a CUDA src_index is range-checked by the kernels that read it (no host cache that an address-reusing
+    allocator could fool): the same storage, first in range, then out of range -- the second call must raise and must not
+    read out of bounds (the bad unit reads source 0)."""
+    frames, depths = clip
+    T1, T2, K, _ = orbit_units(depths[:2], H, W, presets=ORBIT_PRESETS[:1])
+    M = prepare_matrices(T1, T2, K)
+    idx = torch.tensor([0, 1], dtype=torch.int32, device=warper.device)
+    ok = warper.forward_warp_matrices(frames[:2], depths[:2], M, src_index=idx)
+    idx.copy_(torch.tensor([0, 7], dtype=torch.int32))                 # same address, same version-less storage, now out of range
+    with pytest.raises(IndexError):
+        warper.forward_warp_matrices(frames[:2], depths[:2], M, src_index=idx)
+    flag = torch.zeros(1, dtype=torch.int32, device=warper.device)
+    got = warper.forward_warp_matrices(frames[:2], depths[:2], M, src_index=idx, check_range=flag)
+    assert int(flag.item()) & 4
+    assert torch.equal(got[1][0], ok[1][0]) and torch.equal(got[3][0], ok[3][0])      # the in-range unit is untouched

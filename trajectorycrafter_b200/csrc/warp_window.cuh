@@ -48,6 +48,7 @@ struct WinArgs {
     float* flowbuf; float* zbuf; WinBox* box; WinGrp* grp;   // per prep slot
     // K2 products
     int* counter; int* spill_flag; int* slab_off; float* pile;   // per splat slot
+    WinBox* sbox;                                            // per splat slot: the slabs K2 actually wrote (box + offset in `pad`; bw == 0: none)
     float4* pool4; float* poolw; long long pool_cells; int n_slots;
     float4* spill4; float* spillw;
     int* status;                                             // device word: bit 1 = a footprint was reduced into the shared plane, bit 2 = src_index out of range
@@ -280,6 +281,7 @@ enum { WM_SMEM = 0, WM_GLOBAL = 1 };
 struct WinOut {
     // WM_SMEM
     float4* s4; float* sw; unsigned char* tag;
+    int scratch;          // first scratch cell (= cells of the window): lane l may use cell scratch + l
     // WM_GLOBAL: this warp's slab (or the unit's shared plane)
     float4* g4; float* gw;
 };
@@ -329,17 +331,18 @@ __device__ __forceinline__ void emit_window_single(const WinOut& o, int lane, bo
 
 // One corner of one pixel column set, WM_SMEM fast path: the caller has established that no two lanes address the
 // same cell in this step (win_steps_distinct), so the update is a plain read-modify-write of the warp's own window.
-__device__ __forceinline__ void win_step(const WinOut& o, bool on, int id, u64 rg, u64 bz, float w) {
-    if (on) {
-        const int p4 = id + (id >> 3);
-        const float4 a = o.s4[p4];
-        const float s = o.sw[p4];
-        const u64 w2 = pk1(w);
-        float r, g, b, z;
-        upk(fma2(rg, w2, pk(a.x, a.y)), r, g); upk(fma2(bz, w2, pk(a.z, a.w)), b, z);
-        o.s4[p4] = make_float4(r, g, b, z);
-        o.sw[p4] = s + w;
-    }
+__device__ __forceinline__ void win_step(const WinOut& o, int lane, bool on, int id, u64 rg, u64 bz, float w) {
+    // a pixel that adds nothing (its weight and values are 0) goes through the same instructions into its lane's scratch cell:
+    // no divergent branch in the step
+    const int c = on ? id : o.scratch + lane;
+    const int p4 = c + (c >> 3);
+    const float4 a = o.s4[p4];
+    const float s = o.sw[p4];
+    const u64 w2 = pk1(w);
+    float r, g, b, z;
+    upk(fma2(rg, w2, pk(a.x, a.y)), r, g); upk(fma2(bz, w2, pk(a.z, a.w)), b, z);
+    o.s4[p4] = make_float4(r, g, b, z);
+    o.sw[p4] = s + w;
     __syncwarp();
 }
 // live lanes form one run of consecutive lanes?
@@ -516,10 +519,10 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
         upk(wNW2, wNWA, wNWB); upk(wSW2, wSWA, wSWB); upk(wNE2, wNEA, wNEB); upk(wSE2, wSEA, wSEB);
         if (MODE == WM_SMEM && distinct) {
             // eight plain steps in a fixed order: NW, SW, NE, SE of the A pixels and of the B pixels
-            win_step(o, liveA, idNWA, rgA, bzA, wNWA); win_step(o, liveB, idNWB, rgB, bzB, wNWB);
-            win_step(o, liveA, idSWA, rgA, bzA, wSWA); win_step(o, liveB, idSWB, rgB, bzB, wSWB);
-            win_step(o, liveA, idNEA, rgA, bzA, wNEA); win_step(o, liveB, idNEB, rgB, bzB, wNEB);
-            win_step(o, liveA, idSEA, rgA, bzA, wSEA); win_step(o, liveB, idSEB, rgB, bzB, wSEB);
+            win_step(o, lane, liveA, idNWA, rgA, bzA, wNWA); win_step(o, lane, liveB, idNWB, rgB, bzB, wNWB);
+            win_step(o, lane, liveA, idSWA, rgA, bzA, wSWA); win_step(o, lane, liveB, idSWB, rgB, bzB, wSWB);
+            win_step(o, lane, liveA, idNEA, rgA, bzA, wNEA); win_step(o, lane, liveB, idNEB, rgB, bzB, wNEB);
+            win_step(o, lane, liveA, idSEA, rgA, bzA, wSEA); win_step(o, lane, liveB, idSEB, rgB, bzB, wSEB);
             continue;
         }
 
@@ -579,185 +582,6 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
     }
 }
 
-// ------------------------------------------------------------------------------------------------
-// The forward warp's rows in a shared-memory window, lean form.  A row takes the eight plain steps (win_step without
-// the branch) when every pixel of the warp is either "interior" (all four corner cells are real cells) or plainly
-// outside, no pixel sits exactly on padded cell (2,2), and each step addresses 32 different cells; any other row is
-// handed to splat_window_rows (clamped formulas, serialised additions).  Pixels that add nothing go through the same
-// steps with weight 0 into a scratch slot of their own lane (`dummy` + lane), so the row has no divergent branch.
-// Rows are loaded one ahead (two register sets, the loop body is written twice).
-// ------------------------------------------------------------------------------------------------
-struct WinRow { float2 fx, fy, z, r, g, b, m; };      // .x = pixel A (column x0 + 2 lane), .y = pixel B
-
-// loads the compiler may not sink below later volatile statements (the shared-memory steps): a row's loads are issued
-// one row ahead of their use
-__device__ __forceinline__ float2 ld2_cg(const float* p) {
-    float2 v;
-    asm volatile("ld.global.cg.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ float2 ld2_nc(const float* p) {
-    float2 v;
-    asm volatile("ld.global.nc.v2.f32 {%0, %1}, [%2];" : "=f"(v.x), "=f"(v.y) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ float ld1_cg(const float* p) {
-    float v;
-    asm volatile("ld.global.cg.f32 %0, [%1];" : "=f"(v) : "l"(p));
-    return v;
-}
-__device__ __forceinline__ float ld1_nc(const float* p) {
-    float v;
-    asm volatile("ld.global.nc.f32 %0, [%1];" : "=f"(v) : "l"(p));
-    return v;
-}
-
-__device__ __forceinline__ void splat_rows_fused(const WinArgs& A, const WinSrc& S, const WinOut& o, int lane, int x0s, int y0, int y1,
-                                                 bool act, int pitch, int idbase, int cells, float L,
-                                                 u64& hrg, u64& hbz, float& hwt, bool& any_pile) {
-    constexpr unsigned FULL = 0xffffffffu;
-    const int h = A.h, w = A.w;
-    const int xA = x0s + 2 * lane, xB = xA + 1;
-    const bool okA = xA < w && act, okB = xB < w && act;
-    const unsigned hw32 = (unsigned)((size_t)h * w);
-    const u64 fx2 = pk((float)xA, (float)xB), one2 = pk1(1.0f);
-    const int colA = xA < w ? xA : 0, colB = xB < w ? xB : 0;
-    const bool vec2 = xB < w && !(w & 1) &&
-        !((((size_t)S.fl) | ((size_t)S.wd) | ((size_t)S.v[0]) | ((size_t)S.v[1]) | ((size_t)S.v[2]) | ((size_t)S.m1)) & 7);
-    const bool vec2all = __all_sync(FULL, vec2 || !(xA < w));
-    const bool has_m = S.m1 != nullptr;
-    const bool Lok = L >= 9.5367431640625e-07f;
-    float rL = rcp_approx(L);
-    rL = fmaf(rL, fmaf(-L, rL, 1.0f), rL);
-    const u64 rL2 = pk1(rL), nL2 = pk1(-L);
-    const unsigned below = lane ? (1u << (lane - 1)) : 0u;
-    const unsigned s4b = (unsigned)__cvta_generic_to_shared(o.s4), swb = (unsigned)__cvta_generic_to_shared(o.sw);
-    const int dummy_id = cells + lane;
-
-    auto load_row = [&](WinRow& R, int y) {
-        const unsigned q = (unsigned)y * (unsigned)w;
-        if (vec2all) {
-            const unsigned qa = q + colA;
-            R.fx = ld2_cg(S.fl + qa); R.fy = ld2_cg(S.fl + hw32 + qa); R.z = ld2_cg(S.wd + qa);
-            R.r = ld2_nc(S.v[0] + qa); R.g = ld2_nc(S.v[1] + qa); R.b = ld2_nc(S.v[2] + qa);
-            if (has_m) R.m = ld2_nc(S.m1 + qa);
-        } else {
-            const unsigned qa = q + colA, qb = q + colB;
-            R.fx = make_float2(ld1_cg(S.fl + qa), ld1_cg(S.fl + qb)); R.fy = make_float2(ld1_cg(S.fl + hw32 + qa), ld1_cg(S.fl + hw32 + qb));
-            R.z = make_float2(ld1_cg(S.wd + qa), ld1_cg(S.wd + qb));
-            R.r = make_float2(ld1_nc(S.v[0] + qa), ld1_nc(S.v[0] + qb)); R.g = make_float2(ld1_nc(S.v[1] + qa), ld1_nc(S.v[1] + qb));
-            R.b = make_float2(ld1_nc(S.v[2] + qa), ld1_nc(S.v[2] + qb));
-            if (has_m) R.m = make_float2(ld1_nc(S.m1 + qa), ld1_nc(S.m1 + qb));
-        }
-    };
-    // the top and the bottom cell of one column of one pixel: two reads, two writes.  The two cells differ (the caller
-    // sends the bottom one to the scratch slot when the pixel sits on a cell row exactly), and no other lane addresses
-    // either of them in this step.
-    auto step2 = [&](int idT, int idB, u64 rg, u64 bz, float wT, float wB) {
-        const int pT = idT + (idT >> 3), pB = idB + (idB >> 3);
-        const unsigned awT = swb + 4u * (unsigned)pT, a4T = s4b + 16u * (unsigned)pT;
-        const unsigned awB = swb + 4u * (unsigned)pB, a4B = s4b + 16u * (unsigned)pB;
-        float4 a, c;
-        float sa, sc;
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w) : "r"(a4T));
-        asm volatile("ld.shared.v4.f32 {%0, %1, %2, %3}, [%4];" : "=f"(c.x), "=f"(c.y), "=f"(c.z), "=f"(c.w) : "r"(a4B));
-        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sa) : "r"(awT));
-        asm volatile("ld.shared.f32 %0, [%1];" : "=f"(sc) : "r"(awB));
-        const u64 t2 = pk1(wT), b2 = pk1(wB);
-        float r, g, b, z;
-        upk(fma2(rg, t2, pk(a.x, a.y)), r, g); upk(fma2(bz, t2, pk(a.z, a.w)), b, z);
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(a4T), "f"(r), "f"(g), "f"(b), "f"(z) : "memory");
-        upk(fma2(rg, b2, pk(c.x, c.y)), r, g); upk(fma2(bz, b2, pk(c.z, c.w)), b, z);
-        asm volatile("st.shared.v4.f32 [%0], {%1, %2, %3, %4};" :: "r"(a4B), "f"(r), "f"(g), "f"(b), "f"(z) : "memory");
-        asm volatile("st.shared.f32 [%0], %1;" :: "r"(awT), "f"(sa + wT) : "memory");
-        asm volatile("st.shared.f32 [%0], %1;" :: "r"(awB), "f"(sc + wB) : "memory");
-        __syncwarp();
-    };
-    // returns false when the row needs the general routine
-    auto row = [&](const WinRow& R, int y) -> bool {
-        const float fy = (float)y;
-        float oxA, oxB, oyA, oyB;
-        upk(add2(add2(pk(R.fx.x, R.fx.y), fx2), one2), oxA, oxB);
-        upk(add2(add2(pk(R.fy.x, R.fy.y), pk1(fy)), one2), oyA, oyB);
-        const float fx0A = floorf(oxA), fx0B = floorf(oxB), fy0A = floorf(oyA), fy0B = floorf(oyB);
-        const int ix0A = (int)fx0A, ix0B = (int)fx0B, iy0A = (int)fy0A, iy0B = (int)fy0B;
-        // interior: floor cell and its +1 neighbours are real cells (1 .. w, 1 .. h); far: even the floor cell is outside the padded grid
-        const bool inA = okA && (unsigned)(ix0A - 1) < (unsigned)(w - 1) && (unsigned)(iy0A - 1) < (unsigned)(h - 1);
-        const bool inB = okB && (unsigned)(ix0B - 1) < (unsigned)(w - 1) && (unsigned)(iy0B - 1) < (unsigned)(h - 1);
-        const bool farA = !okA || (unsigned)ix0A > (unsigned)w || (unsigned)iy0A > (unsigned)h || !(oxA == oxA) || !(oyA == oyA);
-        const bool farB = !okB || (unsigned)ix0B > (unsigned)w || (unsigned)iy0B > (unsigned)h || !(oxB == oxB) || !(oyB == oyB);
-        const bool dxA = oxA != fx0A, dxB = oxB != fx0B, dyA = oyA != fy0A, dyB = oyB != fy0B;       // ceil == floor + 1 ?
-        const bool pileA = inA && (ix0A | iy0A) == 2 && !dxA && !dyA, pileB = inB && (ix0B | iy0B) == 2 && !dxB && !dyB;
-        bool slow = (!inA && !farA) || (!inB && !farB) || pileA || pileB;
-        const unsigned mA = __ballot_sync(FULL, inA), mB = __ballot_sync(FULL, inB);
-        {   // distinct columns per step (see splat_window_rows): k = 2 ix0 + (ix1 - ix0) grows by >= 2 from live lane to live lane
-            const int kA = 2 * ix0A + (dxA ? 1 : 0), kB = 2 * ix0B + (dxB ? 1 : 0);
-            const int qA = __shfl_up_sync(FULL, kA, 1), qB = __shfl_up_sync(FULL, kB, 1);
-            slow |= (inA && (mA & below) && kA - qA < 2) || (inB && (mB & below) && kB - qB < 2);
-        }
-        if (__any_sync(FULL, slow) || !win_run(mA) || !win_run(mB)) return false;
-        if ((mA | mB) == 0u) return true;                                                  // nothing lands anywhere
-        // ---- soft-z weight mg = mask1 * exp(-50 * log(1 + sat(z)) / L)   (:490-513)
-        u64 mg2;
-        {
-            const u64 ld = log2x(add2(pk(clampf(R.z.x, 0.0f, 1000.0f), clampf(R.z.y, 0.0f, 1000.0f)), one2));
-            u64 qd;
-            if (Lok) qd = div2_with_rcp(ld, nL2, rL2);
-            else qd = pk(__fdiv_rn(plo(ld), L), __fdiv_rn(phi(ld), L));
-            mg2 = exp2x(mul2(qd, pk1(-50.0f)));
-            if (has_m) mg2 = mul2(mg2, pk(R.m.x, R.m.y));
-        }
-        mg2 = pk(inA ? plo(mg2) : 0.0f, inB ? phi(mg2) : 0.0f);
-        // ---- proximity weights (:477-488)
-        const u64 ox2 = pk(oxA, oxB), oy2 = pk(oyA, oyB), fx02 = pk(fx0A, fx0B), fy02 = pk(fy0A, fy0B);
-        const u64 fx12 = add2(fx02, pk(dxA ? 1.0f : 0.0f, dxB ? 1.0f : 0.0f)), fy12 = add2(fy02, pk(dyA ? 1.0f : 0.0f, dyB ? 1.0f : 0.0f));
-        const u64 ax = sub2(one2, sub2(ox2, fx02)), bx = sub2(one2, sub2(fx12, ox2));
-        const u64 ay = sub2(one2, sub2(oy2, fy02)), by = sub2(one2, sub2(fy12, oy2));
-        float wNWA, wNWB, wSWA, wSWB, wNEA, wNEB, wSEA, wSEB;
-        upk(mul2(mul2(ay, ax), mg2), wNWA, wNWB); upk(mul2(mul2(by, ax), mg2), wSWA, wSWB);
-        upk(mul2(mul2(ay, bx), mg2), wNEA, wNEB); upk(mul2(mul2(by, bx), mg2), wSEA, wSEB);
-        // ---- cells.  A pixel that adds nothing uses its lane's scratch slot; so does the bottom cell of a pixel that
-        // sits exactly on a cell row (top and bottom cell are the same cell there: the top one takes both weights)
-        const bool tA = inA && dyA, tB = inB && dyB;
-        const int nwA = inA ? iy0A * pitch + ix0A + idbase : dummy_id, nwB = inB ? iy0B * pitch + ix0B + idbase : dummy_id;
-        const int swA = tA ? nwA + pitch : dummy_id, swB = tB ? nwB + pitch : dummy_id;
-        const int eA = inA && dxA ? 1 : 0, eB = inB && dxB ? 1 : 0;
-        if (!tA) { wNWA += wSWA; wNEA += wSEA; wSWA = 0.0f; wSEA = 0.0f; }
-        if (!tB) { wNWB += wSWB; wNEB += wSEB; wSWB = 0.0f; wSEB = 0.0f; }
-        const u64 rgA = pk(R.r.x, R.g.x), bzA = pk(R.b.x, R.z.x), rgB = pk(R.r.y, R.g.y), bzB = pk(R.b.y, R.z.y);
-        step2(nwA, swA, rgA, bzA, wNWA, wSWA);
-        step2(nwB, swB, rgB, bzB, wNWB, wSWB);
-        step2(nwA + eA, tA ? swA + eA : dummy_id, rgA, bzA, wNEA, wSEA);
-        step2(nwB + eB, tB ? swB + eB : dummy_id, rgB, bzB, wNEB, wSEB);
-        return true;
-    };
-
-    WinRow R0, R1;
-    R0.m = make_float2(1.f, 1.f); R1.m = R0.m;
-    load_row(R0, y0);
-    {   // the window is cleared while the first row's loads are in flight
-        const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
-        const int n4 = cells + (cells >> 3) + 1;
-        for (int i = lane; i < n4; i += 32) o.s4[i] = z4;
-        for (int i = lane; i < n4; i += 32) o.sw[i] = 0.f;
-        __syncwarp();
-    }
-    unsigned later = 0u;                                   // rows left to the general routine, run after the others
-    for (int y = y0; y < y1; y += 2) {
-        if (y + 1 < y1) load_row(R1, y + 1);
-        if (!row(R0, y)) later |= 1u << (y - y0);
-        if (y + 1 < y1) {
-            if (y + 2 < y1) load_row(R0, y + 2);
-            if (!row(R1, y + 1)) later |= 1u << (y + 1 - y0);
-        }
-    }
-    while (later) {
-        const int k = __ffs(later) - 1;
-        later &= later - 1;
-        splat_window_rows<WM_SMEM>(A, S, o, lane, x0s, y0 + k, y0 + k + 1, act, pitch, idbase, L, hrg, hbz, hwt, any_pile);
-    }
-}
-
 __global__ void __launch_bounds__(WIN_WARPS * 32, 3)
 k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     constexpr unsigned FULL = 0xffffffffu;
@@ -775,7 +599,7 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     unsigned char* base = win_smem + (size_t)wv * WIN_BYTES;
     WinOut o;
     o.s4 = (float4*)base; o.sw = (float*)(base + WIN_P4 * 16); o.tag = base + WIN_P4 * 16 + WIN_PW * 4;
-    o.g4 = nullptr; o.gw = nullptr;
+    o.g4 = nullptr; o.gw = nullptr; o.scratch = 0;
 
     // sources of this unit
     WinSrc S;
@@ -805,19 +629,32 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     bool any_pile = false;
     int off0 = -1, off1 = -1;
 
+    // one slab for the whole strip when the union of the two half-strip boxes costs at most a quarter more cells than the two
+    // boxes: the gather then meets one slab instead of two
+    WinBox bu = b0;
+    bool uni = false;
+    if (a0 > 0 && a1 > 0) {
+        const int ux0 = min((int)b0.x0, (int)b1.x0), uy0 = min((int)b0.y0, (int)b1.y0);
+        const int ux1 = max((int)b0.x0 + b0.bw, (int)b1.x0 + b1.bw), uy1 = max((int)b0.y0 + b0.bh, (int)b1.y0 + b1.bh);
+        const int ua = (ux1 - ux0) * (uy1 - uy0);
+        if (ua <= WIN_CAP && 4 * ua <= 5 * (a0 + a1)) {
+            uni = true;
+            bu.x0 = (short)ux0; bu.y0 = (short)uy0; bu.bw = (short)(ux1 - ux0); bu.bh = (short)(uy1 - uy0);
+        }
+    }
     if (a0 + a1 > 0 || ((b0.flags | b1.flags) & 1)) {
         const int half = lane >> 4;
         // passes: both halves in one window if they fit together, else one half per pass
-        const bool together = a0 + a1 <= WIN_CAP;
+        const bool together = uni || a0 + a1 <= WIN_CAP;
         const int npass = together ? 1 : 2;
         for (int p = 0; p < npass; ++p) {
             const bool act0 = together || p == 0, act1 = together || p == 1;
-            const int n0 = act0 ? a0 : 0, n1 = act1 ? a1 : 0, cells = n0 + n1;
+            const int n0 = uni ? (int)bu.bw * bu.bh : (act0 ? a0 : 0), n1 = uni ? 0 : (act1 ? a1 : 0), cells = n0 + n1;
             const bool pile_only = cells == 0;
             if (pile_only && !(((act0 ? b0.flags : 0) | (act1 ? b1.flags : 0)) & 1)) continue;
             // window of this lane's half for this pass
             const bool act = half ? act1 : act0;
-            const WinBox& bm = half ? b1 : b0;
+            const WinBox& bm = uni ? bu : (half ? b1 : b0);
             const int pitch = bm.bw;
             int mode = cells <= WIN_CAP ? WM_SMEM : WM_GLOBAL;
             long long off = 0;
@@ -834,20 +671,20 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
                 idbase = -(w + 1);
                 if (lane == 0) { A.spill_flag[sl] = 1; if (A.status) atomicOr(A.status, 2); }
             } else {
-                idbase = (half && act0 ? n0 : 0) - ((int)bm.y0 + 1) * pitch - ((int)bm.x0 + 1);
+                idbase = (!uni && half && act0 ? n0 : 0) - ((int)bm.y0 + 1) * pitch - ((int)bm.x0 + 1);
                 o.g4 = A.pool4 + (size_t)sl * A.pool_cells + off; o.gw = A.poolw + (size_t)sl * A.pool_cells + off;
             }
             const int pitch_l = shared_plane ? w : pitch;
             if (mode == WM_SMEM) {
-                if (!A.fused) {
+                o.scratch = cells;
+                {
                     const float4 z4 = make_float4(0.f, 0.f, 0.f, 0.f);
                     const int n4 = cells + (cells >> 3) + 1, nw = n4;
                     for (int i = lane; i < n4; i += 32) o.s4[i] = z4;
                     for (int i = lane; i < nw; i += 32) o.sw[i] = 0.f;
                     __syncwarp();
                 }
-                if (A.fused) splat_rows_fused(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, cells, L, hrg, hbz, hwt, any_pile);
-                else splat_window_rows<WM_SMEM>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
+                splat_window_rows<WM_SMEM>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
                 __syncwarp();
                 // the window becomes a dense slab (cells in window order == slab order)
                 for (int i = lane; i < cells; i += 32) {
@@ -865,10 +702,21 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
                 splat_window_rows<WM_GLOBAL>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
             }
             if (!shared_plane) {
-                if (act0 && a0 > 0) off0 = (int)off;
-                if (act1 && a1 > 0) off1 = (int)off + n0;
+                if (uni) off0 = (int)off;
+                else {
+                    if (act0 && a0 > 0) off0 = (int)off;
+                    if (act1 && a1 > 0) off1 = (int)off + n0;
+                }
             }
         }
+    }
+    if (lane < 2) {      // what the gather will find: the slab(s) of this strip
+        WinBox r = lane ? b1 : b0;
+        if (uni) { r = bu; if (lane) r.bw = 0; }
+        const int off = lane ? off1 : off0;
+        if (off < 0) r.bw = 0;
+        r.pad = off;
+        A.sbox[(size_t)sl * A.nh + hs0 + lane] = r;
     }
     if (lane == 0) { offp[0] = off0; offp[1] = off1; }
     // pixels that sat exactly on padded cell (2,2): one sum per strip, added by K3 to output pixel (1,1)
@@ -917,9 +765,8 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
     const int X0 = tx_t * 32, Y0 = ty_t * 32, X1 = X0 + 32 < w ? X0 + 32 : w;
     const int tx = X0 + lane, row0 = Y0 + wv * 8;
     const int R1 = row0 + 8 < h ? row0 + 8 : h;                     // this warp's tile: [X0, X1) x [row0, R1)
-    const WinBox* __restrict__ box = A.box + (size_t)ps * A.nh;
+    const WinBox* __restrict__ box = A.sbox + (size_t)sl * A.nh;          // slabs as K2 wrote them (offset in `pad`)
     const WinGrp* __restrict__ grp = A.grp + (size_t)ps * A.ng;
-    const int* __restrict__ soff = A.slab_off + (size_t)sl * A.nh;
     const float4* __restrict__ p4 = A.pool4 + (size_t)sl * A.pool_cells;
     const float* __restrict__ pw = A.poolw + (size_t)sl * A.pool_cells;
 
@@ -982,7 +829,7 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
                     const int hs = hitl[b + sel] * WIN_GROUP + j;
                     if (hs < A.nh) {
                         const WinBox bx = box[hs];
-                        const int off = soff[hs];
+                        const int off = bx.pad;
                         in = bx.bw > 0 && off >= 0 && bx.x0 < X1 && bx.x0 + bx.bw > X0 && bx.y0 < R1 && bx.y0 + bx.bh > row0;
                         e = make_int4(bx.x0, bx.y0, (int)bx.bw | ((int)bx.bh << 16), off);
                     }
