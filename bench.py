@@ -36,12 +36,11 @@ NCU_TRAFFIC_BYTES_PER_LAUNCH = {"atomic": 238_216_960,   # r1_final_kernels_full
 NCU_DRAM_BYTES_PER_STEP = {"atomic": 3_160_000_000, "window": None}
 # bytes each kernel itself must move per unit pixel (its own inputs + outputs, intermediates included)
 OWN_BYTES_PER_PX = {"window": {"prepass": 16.0, "splat": 44.0, "normalise": 40.0},       # K1: depth in, flow + z' out; K2: flow, z', RGB in, >= 1 slab cell out; K3: >= 1 slab cell in, 20 B out
-                    "atomic": {"prepass": 4.0, "splat": 24.0, "normalise": 40.0},
-                    "integer": {"prepass": 4.0, "splat": 24.0, "normalise": 60.0, "wmax": 16.0}}
+                    "atomic": {"prepass": 4.0, "splat": 24.0, "normalise": 40.0}}
 
 
 ACCUMULATION = {"window": "fixed order: warp-private shared-memory windows + ordered gather (default, reproducible)",
-                "atomic": "fp32 L2 reductions (order varies run to run)", "integer": "int64 fixed point (order-free)"}
+                "atomic": "fp32 L2 reductions (order varies run to run)"}
 
 
 def load_peaks():
@@ -360,7 +359,7 @@ def run_ours(args):
         # bytes that kernel itself must move, and the same kernels inside the timed multi-lane schedule.
         def gbps(bytes_per_px, ms_, units_):
             return bytes_per_px * units_ * H * W / (ms_ * 1e-3) / 1e9
-        kname = {"window": "k_splat_window", "atomic": "k_splat_pair", "integer": "k_splat_pair_det<i64>"}[args.accumulation]
+        kname = {"window": "k_splat_window", "atomic": "k_splat_pair"}[args.accumulation]
         own = OWN_BYTES_PER_PX[args.accumulation]
         tot_i, tot_k = sum(v[0] for v in iso.values()), sum(v[0] for v in prof.values())
         step_gbps = ALGO_BYTES_PER_PX * px_per_step / (ms_local * 1e-3) / 1e9
@@ -437,40 +436,45 @@ def run_ours(args):
         dropin["what"] = ("wall clock incl. the host-side T2*T1^-1 / K^-1 preparation, output allocation and the range-flag read; "
                           "forward_warp_b1_loop_49 is the reference's own call pattern (49 calls with b = 1)")
 
-    # ---- e2e: host buffers through the C-ABI host entry (H2D + kernels + D2H inside the timed region)
+    # ---- e2e: host buffers through the C-ABI host entry (H2D + kernels + D2H inside the timed region).  The step's result is
+    # what every shipped caller keeps of the four outputs (`warped, mask, _, _`, demo.py:78-90): colour float32 + validity
+    # mask, the mask as uint8; depth and flow12 stay on the device.  The all-four-outputs form is timed beside it at N = 1.
     e2e = None
     if not args.no_e2e:
         hf, hd = frames.pin_memory(), depths.pin_memory()
-        houts = (torch.empty((n_units, 3, H, W)).pin_memory(), torch.empty((n_units, 1, H, W)).pin_memory(),
-                 torch.empty((n_units, 1, H, W)).pin_memory(), torch.empty((n_units, 2, H, W)).pin_memory())
         Mh = M.contiguous()
-        warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=houts)
+        hc = (torch.empty((n_units, 3, H, W)).pin_memory(), torch.empty((n_units, 1, H, W), dtype=torch.uint8).pin_memory(), None, None)
+
+        def host_call():
+            return warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=hc, return_depth=False, return_flow=False, mask_u8=True)
+        host_call()
         barrier()
         k_e2e = max(1, min(args.steps, 5))
         t0 = time.perf_counter()
         for _ in range(k_e2e):
-            res = warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=houts)
+            res = host_call()
         dt = (time.perf_counter() - t0) / k_e2e
         assert res[4] == 0
         dt = max_over_ranks(dt)
         e2e = {"value": world * px_per_step / dt / 1e6, "unit": "Mpix/s",
                "h2d_bytes_per_step": int(hf.numel() * 4 + hd.numel() * 4 + Mh.numel() * 4 + src.numel() * 4),
-               "d2h_bytes_per_step": int(sum(t.numel() * 4 for t in houts) + 4),
+               "d2h_bytes_per_step": int(n_units * H * W * 13 + 4),
                "ms_per_step": dt * 1e3, "steps": k_e2e,
-               "api": "Warper.forward_warp_host -> tcw_forward_warp_host (pinned host buffers)"}
-        # what every shipped caller keeps of the four outputs (`warped, mask, _, _`): colour + mask, the mask as uint8
+               "api": "Warper.forward_warp_host(return_depth=False, return_flow=False, mask_u8=True) -> tcw_forward_warp_host "
+                      "(pinned host buffers in, colour f32 + mask u8 out)"}
         if rank == 0 and world == 1:
-            hc = (houts[0], torch.empty((n_units, 1, H, W), dtype=torch.uint8).pin_memory(), None, None)
-            warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=hc, return_depth=False, return_flow=False, mask_u8=True)
+            houts = (hc[0], torch.empty((n_units, 1, H, W)).pin_memory(),
+                     torch.empty((n_units, 1, H, W)).pin_memory(), torch.empty((n_units, 2, H, W)).pin_memory())
+            warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=houts)
             t0 = time.perf_counter()
             for _ in range(k_e2e):
-                warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=hc, return_depth=False, return_flow=False, mask_u8=True)
-            dtc = (time.perf_counter() - t0) / k_e2e
-            e2e["condition_only"] = {"value": px_per_step / dtc / 1e6, "ms_per_step": dtc * 1e3,
-                                     "d2h_bytes_per_step": int(n_units * H * W * 13 + 4),
-                                     "what": "colour f32 + mask u8 only (depth and flow12 stay on the device)"}
-            del hc
-        del houts
+                warper.forward_warp_host(hf, hd, Mh, src_index=src, outputs=houts)
+            dta = (time.perf_counter() - t0) / k_e2e
+            e2e["all_four_outputs"] = {"value": px_per_step / dta / 1e6, "ms_per_step": dta * 1e3,
+                                       "d2h_bytes_per_step": int(sum(t.numel() * 4 for t in houts) + 4),
+                                       "what": "colour, mask, depth and flow12 as float32, the reference signature's full 4-tuple"}
+            del houts
+        del hc
 
     # ---- multi-GPU as the path is specified: ONE clip's 392 units sharded over the ranks (strong scaling), then the same
     # with the exchange inside the timed step -- colour float32 + mask uint8 (13 B per pixel) of ALL units on rank 0:
@@ -571,6 +575,52 @@ def run_ours(args):
                 "note": "includes the two torch.empty output allocations of the Python entry; 462 MB in + 202 MB out, larger than L2"}
         del pf, pm
 
+    # ---- the other SURVEY 8(f) rows, reported beside the metric, never part of it
+    extras = None
+    if rank == 0 and world == 1 and not args.no_extras:
+        extras = {}
+        from trajectorycrafter_b200 import GlobalPointCloudWarper
+        from trajectorycrafter_b200.workloads import orbit_units as _ou
+
+        def dev_time(fn, reps):
+            fn(); torch.cuda.synchronize()
+            a, b = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+            a.record()
+            for _ in range(reps):
+                fn()
+            b.record()
+            torch.cuda.synchronize()
+            return a.elapsed_time(b) / reps
+        # A6 / N3: forward_warp(twice=True) = five chained splats (models/utils.py:296-347), one 384x672 frame per call
+        tT1, tT2, tK, _ = _ou(depths[:1], H, W, presets=[(0, 12)])
+        f1, d1 = frames_d[:1], depths_d[:1]
+        t_ms = dev_time(lambda: warper.forward_warp(f1, None, d1, tT1, tT2, tK, None, twice=True), 5)
+        extras["twice"] = {"ms_per_frame": t_ms, "Mpix_per_s": H * W / (t_ms * 1e-3) / 1e6,
+                           "what": "Warper.forward_warp(twice=True), b = 1, 384x672: forward colour + depth splat, flow splat, two backward "
+                                   "splats, incl. the host-side matrix preparation of each call"}
+        # N2: z-buffer renderer, 1 M points -> 576x1024 (point_size 2: nine footprint entries per point)
+        pc = GlobalPointCloudWarper(device=f"cuda:{local}")
+        g = torch.Generator().manual_seed(9)
+        n_pts = 1_000_000
+        P = (torch.rand((n_pts, 3), generator=g) * torch.tensor([8.0, 5.0, 6.0]) - torch.tensor([4.0, 2.5, -4.0])).to(dev)
+        C = (torch.rand((n_pts, 3), generator=g) * 2 - 1).to(dev)
+        Tt = torch.eye(4)[None]
+        Kt = torch.tensor([[500.0, 0, 512.0], [0, 500.0, 288.0], [0, 0, 1]])[None]
+        z_ms = dev_time(lambda: pc.render_pointcloud_zbuffer_vectorized_point_size(P, C, Tt, Kt, (576, 1024), 2), 20)
+        z_bytes = n_pts * 24 + 576 * 1024 * (8 + 8 + 16)          # points + colours in; z-buffer cleared + resolved, frame + mask out
+        extras["pointcloud_zbuffer"] = {"ms": z_ms, "Mpoints_per_s": n_pts / (z_ms * 1e-3) / 1e6, "algorithmic_bytes": z_bytes,
+                                        "achieved_GBps": z_bytes / (z_ms * 1e-3) / 1e9, "frac_of_hbm_peak": z_bytes / (z_ms * 1e-3) / 1e9 / peak,
+                                        "what": "render_pointcloud_zbuffer_vectorized_point_size, 1 M points, point_size 2, 576x1024, incl. the "
+                                                "Python entry; 9 M 64-bit atomicMin per call, so the bound is L2 atomics, not HBM"}
+        # N4: depth post-processing of one 49x576x1024 clip (the reference's native depth resolution)
+        res = torch.rand((N_FRAMES, 576, 1024, 3), generator=g).to(dev)
+        p_ms = dev_time(lambda: warper.depth_postprocess(res), 10)
+        p_bytes = N_FRAMES * 576 * 1024 * (12 + 12 + 4)
+        extras["depth_post"] = {"ms": p_ms, "algorithmic_bytes": p_bytes, "achieved_GBps": p_bytes / (p_ms * 1e-3) / 1e9,
+                                "frac_of_hbm_peak": p_bytes / (p_ms * 1e-3) / 1e9 / peak,
+                                "what": "tcw_depth_post on 49x576x1024x3: two reads of the raw output (min/max pass, then the post-processing), one write"}
+        del P, C, res
+
     # ---- CPU baseline (rank 0, N=1 only), bounded samples of the same workload on the box's host cores:
     # the reference's own torch path (oracle/_ref, BASELINE.md section 5: all cores default / deterministic / one thread)
     # and the C port of the same arithmetic (all cores, one full step)
@@ -616,6 +666,8 @@ def run_ours(args):
             line["clip49"] = clip49
         if dropin is not None:
             line["dropin"] = dropin
+        if extras is not None:
+            line["next_rows"] = extras
         if strong is not None:
             line["strong"] = strong
             line["with_gather"] = with_gather

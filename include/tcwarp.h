@@ -29,9 +29,8 @@ extern "C" {
 /* flags */
 #define TCW_PER_UNIT_MAX   1   /* soft-z normaliser log_depth.max() taken per unit (== n_units reference calls with b=1);
                                   without it the max is over the whole call (== one reference call with b=n_units, models/utils.py:492) */
-#define TCW_DETERMINISTIC  2   /* tcw_forward_warp: strict integer accumulation (per-cell maximum weight, then order-free int64 fixed-point sums).
-                                  Slow; the DEFAULT path (no mode flag) is already reproducible run to run: it sums every cell in a fixed order
-                                  (warp-private shared-memory windows, then an ordered gather) */
+/* 2 is retired: the round-1 int64 fixed-point mode.  The DEFAULT path (no mode flag) sums every target cell in a fixed order
+   (warp-private shared-memory windows, then an ordered gather) and is bitwise reproducible */
 #define TCW_CLEAN          4   /* fuse clean_points (models/utils.py:585-626): 5x5 dilation of the hole mask; out_frame/out_mask are then DOUBLE (float64) buffers */
 #define TCW_IS_IMAGE       8   /* tcw_splat only: holes = -1, range check, clamp to [-1,1] (models/utils.py:572-582) */
 #define TCW_ATOMIC_F32    16   /* tcw_forward_warp: opt-in float reductions into L2 accumulators (the round-1 kernel); the order of the
@@ -45,7 +44,8 @@ extern "C" {
 /* bits of *range_flag (status word) */
 #define TCW_STATUS_RANGE       1   /* a valid colour left [-1.1, 1.1] before the clamp: the reference's assert (models/utils.py:580-581) */
 #define TCW_STATUS_UNORDERED   2   /* a footprint did not fit the unit's slab pool and was reduced with float atomics (order not fixed) */
-#define TCW_STATUS_SRC_INDEX   4   /* src_index held a value outside [0, n_src); that unit read source 0 instead */
+#define TCW_STATUS_SRC_INDEX   4
+#define TCW_STATUS_BOUNDS      8   /* -DTCW_BOUNDS_CHECK=1 builds only: an access left its allocation and was skipped */   /* src_index held a value outside [0, n_src); that unit read source 0 instead */
 
 /* error codes */
 #define TCW_OK              0
@@ -68,7 +68,7 @@ long long tcw_launch_count(const tcw_ctx* ctx);
  * Optional per-kernel device timing (CUDA events around every launch, on the launching stream).
  * tcw_profile_read synchronises on the recorded events, sums them per kernel class
  * [0]=pre-pass (default path: project + flow + boxes; opt-in modes: depth-max), [1]=splat, [2]=gather / normalise,
- * [3]=max-weight pre-pass of the integer mode, and resets the log.  ms/launches/units are arrays of 4; units = number of warp units those launches processed.
+ * [3]=unused, and resets the log.  ms/launches/units are arrays of 4; units = number of warp units those launches processed.
  */
 int tcw_profile_enable(tcw_ctx* ctx, int enable);
 int tcw_profile_read(tcw_ctx* ctx, double* ms, long long* launches, double* units);
@@ -84,7 +84,7 @@ int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, int flags
  *   out_frame (n_units,3,h,w)  out_mask (n_units,1,h,w)  out_depth (n_units,1,h,w) or NULL
  *   out_flow (n_units,2,h,w) or NULL
  *   range_flag: device int, OR-ed with TCW_STATUS_* bits (bit 0 = the reference's range assert, :580-581); may be NULL.
- *   flags: TCW_PER_UNIT_MAX, TCW_CLEAN, and at most one mode flag (TCW_DETERMINISTIC | TCW_ATOMIC_F32).
+ *   flags: TCW_PER_UNIT_MAX, TCW_CLEAN, TCW_MASK_U8, and the opt-in mode flag TCW_ATOMIC_F32.
  */
 int tcw_forward_warp(tcw_ctx* ctx,
                      const float* frame, const float* mask1, const float* depth,

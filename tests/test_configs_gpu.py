@@ -246,3 +246,19 @@ def test_src_index_is_checked_on_the_device(warper, clip):
     got = warper.forward_warp_matrices(frames[:2], depths[:2], M, src_index=idx, check_range=flag)
     assert int(flag.item()) & 4
     assert torch.equal(got[1][0], ok[1][0]) and torch.equal(got[3][0], ok[3][0])      # the in-range unit is untouched
+
+
+@pytest.mark.parametrize("mode", ["window", "atomic"])
+@pytest.mark.parametrize("shape", [(75, 131), (76, 131), (75, 130), (33, 65)])
+def test_odd_sizes_vs_oracle(warper, shape, mode):
+    """Odd heights / widths (h * w not a multiple of 4): every mode, with mask1 holes and a camera that puts part of the
+    image behind itself.  Regression for a misaligned accumulator lane of the float-reduction mode found by the sanitizer run."""
+    h, w = shape
+    frames, depths = synthetic_clip(2, h, w, seed=3)
+    T1, T2, K, src = orbit_units(depths, h, w, presets=[(0, 60), (25, 170)])
+    M = prepare_matrices(T1, T2, K)
+    g = torch.Generator().manual_seed(1)
+    mask1 = (torch.rand((2, 1, h, w), generator=g) > 0.2).float()
+    got = warper.forward_warp_matrices(frames, depths, M, src_index=src, mask1=mask1, accumulation=mode)
+    ref = oracle.forward_warp(frames, mask1, depths, M, src_index=src.numpy(), per_unit_max=True)
+    check(got, ref, f"odd {h}x{w} {mode}")

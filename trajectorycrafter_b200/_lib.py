@@ -10,7 +10,6 @@ LIB_PATH = os.environ.get("TCW_LIB", os.path.join(HERE, "libtcwarp.so"))   # TCW
 
 # flags (include/tcwarp.h)
 TCW_PER_UNIT_MAX = 1
-TCW_DETERMINISTIC = 2
 TCW_CLEAN = 4
 TCW_IS_IMAGE = 8
 TCW_ATOMIC_F32 = 16
@@ -21,6 +20,7 @@ TCW_IPC_HANDLE_BYTES = 64
 TCW_STATUS_RANGE = 1
 TCW_STATUS_UNORDERED = 2
 TCW_STATUS_SRC_INDEX = 4
+TCW_STATUS_BOUNDS = 8
 VERSION = 200
 
 # every symbol include/tcwarp.h declares: name -> (restype, argtypes)

@@ -315,18 +315,8 @@ static size_t align_up(size_t v, size_t a) { return (v + a - 1) / a * a; }
 constexpr size_t CTRL_BYTES = 256;
 static size_t header_bytes(int n_units) { return CTRL_BYTES + align_up((size_t)(n_units + 1) * sizeof(UnitStats), 256); }
 
-// accumulator bytes per pixel of one unit: atomic fp32 path 5 planes x 4 B; integer path 5 x int64 + max-weight plane
-static size_t acc_bytes_per_px(int flags) { return (flags & TCW_DETERMINISTIC) ? (size_t)NCH * 8 + 4 : (size_t)NCH * 4; }
-
-// units per chunk of the single-stream loop (integer mode): keep one chunk's accumulators + inputs + outputs inside a fraction of L2
-static int auto_chunk_units(const tcw_ctx* ctx, int n_units, int h, int w, size_t acc_per_px) {
-    if (ctx->chunk_units_override > 0) return ctx->chunk_units_override < n_units ? ctx->chunk_units_override : n_units;
-    const size_t per_unit = (size_t)h * w * (acc_per_px + 44);
-    size_t budget = ctx->l2_bytes ? ctx->l2_bytes * 6 / 10 : (size_t)64 << 20;
-    int g = (int)(budget / per_unit);
-    if (g < 1) g = 1;
-    return g < n_units ? g : n_units;
-}
+// accumulator bytes per pixel of one unit (float-reduction mode): 5 planes x 4 B
+static size_t acc_bytes_per_px(int) { return (size_t)NCH * 4; }
 
 // lanes x units-per-chunk of the multi-stream schedules.  Units in flight = lanes * chunk: what they write and read
 // again (accumulators or slabs, flow, z') should stay L2-resident next to the streaming traffic.  `bytes_per_px` is
@@ -525,13 +515,10 @@ TCW_API int tcw_workspace_bytes(const tcw_ctx* ctx, int n_units, int h, int w, i
     if (!ctx || !bytes || n_units <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_workspace_bytes: bad argument");
     const size_t hw = (size_t)h * w;
     size_t need;
-    if (flags & TCW_DETERMINISTIC) {
-        const int g = auto_chunk_units(ctx, n_units, h, w, acc_bytes_per_px(flags));
-        need = header_bytes(n_units) + align_up((size_t)g * acc_bytes_per_px(flags) * hw, 256);
-    } else if (flags & TCW_ATOMIC_F32) {
+    if (flags & TCW_ATOMIC_F32) {
         int nl = 1, g2 = 1;
         lanes_plan(ctx, n_units, hw, ATOMIC_BYTES_PER_PX, &nl, &g2);
-        need = header_bytes(n_units) + align_up((size_t)nl * g2 * acc_bytes_per_px(flags) * hw, 256);
+        need = header_bytes(n_units) + (size_t)nl * align_up((size_t)g2 * acc_bytes_per_px(flags) * hw, 256);
     } else {
         WinLayout L;
         win_layout(ctx, n_units, h, w, flags, &L);
@@ -553,12 +540,13 @@ static int atomic_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, 
     char* accbase = (char*)workspace + hdr;
     const bool per_unit = flags & TCW_PER_UNIT_MAX;
     const int sidx = per_unit ? -1 : n_units;
-    const int cap = (int)((workspace_bytes - hdr) / unit_bytes);          // units the workspace can hold
     int NL = 1, g2 = 1;
     lanes_plan(ctx, n_units, hw, ATOMIC_BYTES_PER_PX, &NL, &g2);
-    if (NL > cap) NL = cap > 0 ? cap : 1;
-    if (g2 > cap / NL) g2 = cap / NL;
-    if (g2 < 1) return fail(TCW_E_WORKSPACE, "tcw_forward_warp: workspace too small (see tcw_workspace_bytes)");
+    // shrink the plan until its lane buffers (each padded to 256 B) fit the caller's workspace
+    auto fits = [&](int nl, int g) { return hdr + (size_t)nl * align_up((size_t)g * unit_bytes, 256) <= workspace_bytes; };
+    while (g2 > 1 && !fits(NL, g2)) --g2;
+    while (NL > 1 && !fits(NL, g2)) --NL;
+    if (!fits(NL, g2)) return fail(TCW_E_WORKSPACE, "tcw_forward_warp: workspace too small (see tcw_workspace_bytes)");
     int rc = ensure_lanes(ctx, NL);
     if (rc) return rc;
     CUDA_TRY(cudaMemsetAsync(workspace, 0, hdr, st));
@@ -580,9 +568,8 @@ static int atomic_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, 
     B.h = h; B.w = w; B.strips_x = (w + PAIR_W - 1) / PAIR_W;
     B.strips_per_unit = B.strips_x * ((h + PAIR_H_CHUNK - 1) / PAIR_H_CHUNK);
     B.stats = stats; B.stat_index_global = sidx; B.out_flow = out_flow;
-    B.acc_i64 = nullptr; B.wmax = nullptr; B.det_scale = 0.f;
     const int pb = (B.strips_per_unit + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32);
-    const size_t buf_bytes = (size_t)g2 * NCH * hw * sizeof(float);      // buffer b: [g2][hw] float4 then [g2][hw] float
+    const size_t buf_bytes = align_up((size_t)g2 * NCH * hw * sizeof(float), 256);      // buffer b: [g2][hw] float4 then [g2][hw] float; 16-byte aligned for odd h*w too
     // independent lanes: chunk k runs splat + normalise on stream k % NL with buffer k % NL; the normalise kernel
     // re-zeroes what it read, so one memset per call is enough
     CUDA_TRY(cudaMemsetAsync(accbase, 0, (size_t)NL * buf_bytes, st));
@@ -620,64 +607,6 @@ static int atomic_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, 
     return TCW_OK;
 }
 
-// integer path (TCW_DETERMINISTIC): per-cell maximum weight, then order-free fixed-point sums; one stream, chunk by chunk
-static int integer_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
-                           const int* src_index, const float* M, int n_units, int n_src, int h, int w,
-                           int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
-                           int* range_flag, void* workspace, size_t workspace_bytes, cudaStream_t st) {
-    const size_t hw = (size_t)h * w;
-    const size_t hdr = header_bytes(n_units);
-    const size_t unit_bytes = acc_bytes_per_px(flags) * hw;
-    int g = (int)((workspace_bytes - hdr) / unit_bytes);
-    const int want = auto_chunk_units(ctx, n_units, h, w, acc_bytes_per_px(flags));
-    if (g > want) g = want;
-    UnitStats* stats = (UnitStats*)((char*)workspace + CTRL_BYTES);
-    char* accbase = (char*)workspace + hdr;
-    long long* acc_i64 = (long long*)accbase;                              // [g][5][hw] int64 then [g][hw] uint32 max-weight bits
-    unsigned* wmax = (unsigned*)(accbase + (size_t)g * NCH * hw * sizeof(long long));
-    const bool per_unit = flags & TCW_PER_UNIT_MAX, clean = flags & TCW_CLEAN;
-    const int sidx = per_unit ? -1 : n_units;
-    const int tiles_x = (w + TILE_W - 1) / TILE_W, tiles_y = (h + TILE_H - 1) / TILE_H;
-    CUDA_TRY(cudaMemsetAsync(workspace, 0, hdr, st));
-    const int quads = h * ((w + 3) / 4);
-    int k0_bx = (quads + TILE_THREADS * 2 - 1) / (TILE_THREADS * 2);
-    if (k0_bx < 1) k0_bx = 1;
-    for (int u0 = 0; u0 < n_units; u0 += 65535) {
-        const int nu = n_units - u0 < 65535 ? n_units - u0 : 65535;
-        prof_begin(ctx, PK_ZMAX, nu, st);
-        k_zmax_quad<<<dim3(k0_bx, nu), TILE_THREADS, 0, st>>>(depth, src_index, M, u0, n_src, h, w, stats, n_units, 1);
-        prof_end(ctx, st);
-        LAUNCH_CHECK("k_zmax_quad");
-    }
-    PairArgs B;
-    B.frame = frame; B.mask1 = mask1; B.depth = depth; B.src_index = src_index; B.Mall = M; B.n_src = n_src; B.status = range_flag;
-    B.h = h; B.w = w; B.strips_x = (w + PAIR_W - 1) / PAIR_W;
-    B.strips_per_unit = B.strips_x * ((h + PAIR_H_CHUNK - 1) / PAIR_H_CHUNK);
-    B.stats = stats; B.stat_index_global = sidx; B.acc4 = nullptr; B.accw = nullptr; B.out_flow = out_flow;
-    B.acc_i64 = acc_i64; B.wmax = wmax; B.det_scale = ldexpf(1.0f, det_shift(h, w));
-    for (int u0 = 0; u0 < n_units; u0 += g) {
-        const int nu = n_units - u0 < g ? n_units - u0 : g;
-        const dim3 pgrid((B.strips_per_unit + PAIR_THREADS / 32 - 1) / (PAIR_THREADS / 32), nu);
-        CUDA_TRY(cudaMemsetAsync(acc_i64, 0, (size_t)nu * NCH * hw * sizeof(long long), st));
-        CUDA_TRY(cudaMemsetAsync(wmax, 0, (size_t)nu * hw * sizeof(unsigned), st));
-        prof_begin(ctx, PK_WMAX, nu, st);
-        k_splat_pair_det<MODE_WMAX><<<pgrid, PAIR_THREADS, 0, st>>>(B, u0);
-        prof_end(ctx, st);
-        LAUNCH_CHECK("k_splat_pair_det<wmax>");
-        prof_begin(ctx, PK_SPLAT, nu, st);
-        k_splat_pair_det<MODE_I64><<<pgrid, PAIR_THREADS, 0, st>>>(B, u0);
-        prof_end(ctx, st);
-        LAUNCH_CHECK("k_splat_pair_det<i64>");
-        prof_begin(ctx, PK_NORMALISE, nu, st);
-        const dim3 grid(tiles_x * tiles_y, nu);
-        if (clean) k_normalise<true, true><<<grid, TILE_THREADS, 0, st>>>(nullptr, nullptr, acc_i64, stats, sidx, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
-        else       k_normalise<false, true><<<grid, TILE_THREADS, 0, st>>>(nullptr, nullptr, acc_i64, stats, sidx, u0, h, w, tiles_x, out_frame, out_mask, out_depth, range_flag);
-        prof_end(ctx, st);
-        LAUNCH_CHECK("k_normalise");
-    }
-    return TCW_OK;
-}
-
 static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
                                 const int* src_index, const float* M, int n_units, int n_src, int h, int w,
                                 int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
@@ -686,19 +615,15 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
     if (!frame || !depth || !M || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_forward_warp: NULL buffer");
     if (n_units <= 0 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp: bad shape");
     if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp: src_index is NULL but n_src != n_units");
-    if ((flags & TCW_DETERMINISTIC) && (flags & TCW_ATOMIC_F32)) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_DETERMINISTIC and TCW_ATOMIC_F32 exclude each other");
     if ((flags & TCW_ATOMIC_F32) && (flags & TCW_CLEAN)) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_ATOMIC_F32 has no fused clean_points");
-    if ((flags & TCW_MASK_U8) && (flags & (TCW_CLEAN | TCW_ATOMIC_F32 | TCW_DETERMINISTIC)))
+    if ((flags & TCW_MASK_U8) && (flags & (TCW_CLEAN | TCW_ATOMIC_F32)))
         return fail(TCW_E_ARG, "tcw_forward_warp: TCW_MASK_U8 needs the default mode without TCW_CLEAN");
     const size_t hw = (size_t)h * w;
     if (hw >= 0x7fffffffull / 4) return fail(TCW_E_ARG, "tcw_forward_warp: image too large for this build");
     cudaStream_t st = (cudaStream_t)cuda_stream;
-    if (flags & (TCW_DETERMINISTIC | TCW_ATOMIC_F32)) {
+    if (flags & TCW_ATOMIC_F32) {
         if (!workspace || workspace_bytes < header_bytes(n_units) + acc_bytes_per_px(flags) * hw)
             return fail(TCW_E_WORKSPACE, "tcw_forward_warp: workspace too small (see tcw_workspace_bytes)");
-        if (flags & TCW_DETERMINISTIC)
-            return integer_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask, out_depth, out_flow,
-                                   range_flag, workspace, workspace_bytes, st);
         return atomic_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask, out_depth, out_flow,
                               range_flag, workspace, workspace_bytes, st);
     }
@@ -723,7 +648,7 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
                              int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
     if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp: ctx is NULL");
     cudaStream_t st = (cudaStream_t)cuda_stream;
-    bool eligible = !ctx->graphs_off && !ctx->prof_on && !(flags & TCW_DETERMINISTIC);
+    bool eligible = !ctx->graphs_off && !ctx->prof_on;
     if (eligible) {
         cudaStreamCaptureStatus cs = cudaStreamCaptureStatusNone;
         if (cudaStreamIsCapturing(st, &cs) != cudaSuccess || cs != cudaStreamCaptureStatusNone) { cudaGetLastError(); eligible = false; }

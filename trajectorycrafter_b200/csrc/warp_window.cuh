@@ -18,6 +18,17 @@
 // Lanes that hit the same cell in ONE step are serialised through a tag array (see emit_window).
 #pragma once
 
+// -DTCW_BOUNDS_CHECK=1 (scripts/r2_checked.sh): every window / slab / pool access of the default path is range-checked, an
+// access outside its allocation is SKIPPED and status bit 8 is raised.  compute-sanitizer is closed on the measurement pool, so
+// this build is the memory-safety evidence; the product build compiles the checks away.
+#ifndef TCW_BOUNDS_CHECK
+#define TCW_BOUNDS_CHECK 0
+#endif
+#if TCW_BOUNDS_CHECK
+#define TCW_INRANGE(st, cond) ((cond) ? true : (((st) ? (void)atomicOr((st), 8) : (void)0), false))
+#else
+#define TCW_INRANGE(st, cond) true
+#endif
 #ifndef TCW_WIN_CAP
 #define TCW_WIN_CAP 768            // cells of shared-memory window per warp (both half-strips together)
 #endif
@@ -281,6 +292,7 @@ enum { WM_SMEM = 0, WM_GLOBAL = 1 };
 struct WinOut {
     // WM_SMEM
     float4* s4; float* sw; unsigned char* tag;
+    int* status; int glimit;      // checked builds: the call's status word; cells of the global slab / plane o.g4 points at
     int scratch;          // first scratch cell (= cells of the window): lane l may use cell scratch + l
     // WM_GLOBAL: this warp's slab (or the unit's shared plane)
     float4* g4; float* gw;
@@ -295,7 +307,7 @@ template <int MODE>
 __device__ __forceinline__ void emit_window(const WinOut& o, int lane, int id, u64 rg, u64 bz, float sw) {
     constexpr unsigned FULL = 0xffffffffu;
     if (MODE == WM_GLOBAL) {
-        if (id >= 0) {
+        if (id >= 0 && TCW_INRANGE(o.status, id < o.glimit)) {
             float r, g, b, z;
             upk(rg, r, g); upk(bz, b, z);
             asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};\n\t"
@@ -304,7 +316,7 @@ __device__ __forceinline__ void emit_window(const WinOut& o, int lane, int id, u
         }
         return;
     }
-    bool pend = id >= 0;
+    bool pend = id >= 0 && TCW_INRANGE(o.status, id < o.scratch);
     if (!__any_sync(FULL, pend)) return;
     const int p4 = id + (id >> 3), pw = p4;
     do {
@@ -334,7 +346,7 @@ __device__ __forceinline__ void emit_window_single(const WinOut& o, int lane, bo
 __device__ __forceinline__ void win_step(const WinOut& o, int lane, bool on, int id, u64 rg, u64 bz, float w) {
     // a pixel that adds nothing (its weight and values are 0) goes through the same instructions into its lane's scratch cell:
     // no divergent branch in the step
-    const int c = on ? id : o.scratch + lane;
+    const int c = (on && TCW_INRANGE(o.status, (unsigned)id < (unsigned)o.scratch)) ? id : o.scratch + lane;
     const int p4 = c + (c >> 3);
     const float4 a = o.s4[p4];
     const float s = o.sw[p4];
@@ -599,7 +611,7 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     unsigned char* base = win_smem + (size_t)wv * WIN_BYTES;
     WinOut o;
     o.s4 = (float4*)base; o.sw = (float*)(base + WIN_P4 * 16); o.tag = base + WIN_P4 * 16 + WIN_PW * 4;
-    o.g4 = nullptr; o.gw = nullptr; o.scratch = 0;
+    o.g4 = nullptr; o.gw = nullptr; o.scratch = 0; o.status = A.status; o.glimit = 0;
 
     // sources of this unit
     WinSrc S;
@@ -667,12 +679,13 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
             int idbase;
             if (shared_plane) {
                 // the unit's shared accumulation plane: global cell ids, float reductions (order not fixed) -- flagged
-                o.g4 = A.spill4 + (size_t)sl * hw; o.gw = A.spillw + (size_t)sl * hw;
+                o.g4 = A.spill4 + (size_t)sl * hw; o.gw = A.spillw + (size_t)sl * hw; o.glimit = (int)hw;
                 idbase = -(w + 1);
                 if (lane == 0) { A.spill_flag[sl] = 1; if (A.status) atomicOr(A.status, 2); }
             } else {
                 idbase = (!uni && half && act0 ? n0 : 0) - ((int)bm.y0 + 1) * pitch - ((int)bm.x0 + 1);
-                o.g4 = A.pool4 + (size_t)sl * A.pool_cells + off; o.gw = A.poolw + (size_t)sl * A.pool_cells + off;
+                o.g4 = A.pool4 + (size_t)sl * A.pool_cells + off; o.gw = A.poolw + (size_t)sl * A.pool_cells + off; o.glimit = cells;
+                (void)TCW_INRANGE(A.status, off >= 0 && off + cells <= A.pool_cells && cells + WIN_SCRATCH <= WIN_CAP + WIN_SCRATCH + (mode == WM_GLOBAL ? (1 << 30) : 0));
             }
             const int pitch_l = shared_plane ? w : pitch;
             if (mode == WM_SMEM) {
@@ -793,7 +806,7 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
             float sw[8];
             #pragma unroll
             for (int r = 0; r < 8; ++r) {
-                const unsigned cu = ((unsigned)(r0 + r) < (unsigned)bh && colin) ? (unsigned)ci : zero_cell;
+                const unsigned cu = ((unsigned)(r0 + r) < (unsigned)bh && colin && TCW_INRANGE(N.range_flag, (unsigned)ci < (unsigned)A.pool_cells)) ? (unsigned)ci : zero_cell;
                 s4[r] = __ldcg((const float4*)(b4 + (size_t)cu * 16u));
                 sw[r] = __ldcg((const float*)(b1 + (size_t)cu * 4u));
                 ci += bw;

@@ -109,8 +109,7 @@ class Warper:
         Returns (warped (n,3,h,w), mask (n,1,h,w), depth (n,1,h,w)|None, flow12 (n,2,h,w)|None);
         warped/mask are float64 when ``mask=True`` (reference quirk, models/utils.py:618-626).
         ``accumulation``: "window" (default: every target cell is summed in a fixed order, results are bitwise
-        reproducible), "integer" (strict order-free int64 sums, slow) or "atomic" (float reductions in L2,
-        last bits vary from run to run).
+        reproducible) or "atomic" (float reductions in L2, last bits vary from run to run).
         """
         n = transformation1.shape[0]
         M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
@@ -150,7 +149,7 @@ class Warper:
         frames_d, depths_d, mask1_d = self._dev(frames), self._dev(depths), self._dev(mask1)
         M_d = M.to(self.device, torch.float32, non_blocking=True).contiguous()
         si_d = None if src_index is None else src_index.to(self.device, torch.int32).contiguous()
-        mode = {"window": 0, "integer": _lib.TCW_DETERMINISTIC, "atomic": _lib.TCW_ATOMIC_F32}[accumulation]
+        mode = {"window": 0, "atomic": _lib.TCW_ATOMIC_F32}[accumulation]
         flags = (_lib.TCW_PER_UNIT_MAX if per_frame_max else 0) | (_lib.TCW_CLEAN if mask else 0) | mode \
             | (_lib.TCW_MASK_U8 if mask_u8 else 0)
         odt = torch.float64 if mask else torch.float32
@@ -189,6 +188,8 @@ class Warper:
         """Raise for the status bits a call ORs into its flag word (include/tcwarp.h TCW_STATUS_*)."""
         if status & _lib.TCW_STATUS_SRC_INDEX:
             raise IndexError("src_index holds a value outside [0, n_src)")
+        if status & _lib.TCW_STATUS_BOUNDS:      # only a -DTCW_BOUNDS_CHECK=1 build can raise it
+            raise RuntimeError("bounds-checked build: a window / slab access left its allocation")
         # the reference asserts -1.1 <= warped <= 1.1 before clipping (models/utils.py:580-581)
         assert not (status & _lib.TCW_STATUS_RANGE), "warped colour left [-1.1, 1.1]"
 
