@@ -31,9 +31,10 @@ N_FRAMES, H, W = 49, 384, 672
 # (profiles/), for the 24-unit launch shape the roofline figure is quoted on
 # dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel (ncu --set full, profiles/)
 NCU_TRAFFIC_BYTES_PER_LAUNCH = {"atomic": 238_216_960,   # r1_final_kernels_full_24units_ncu.txt: k_splat_pair, 24 units
-                                "window": None}
+                                "window": 208_428_288}    # r2_kernels_full_24units_ncu.txt: k_splat_window, 24 units: 67.6 MB read + 140.8 MB written
 # DRAM bytes of one whole step from the ncu launch list / full captures of the timed schedule (profiles/), per mode
-NCU_DRAM_BYTES_PER_STEP = {"atomic": 3_160_000_000, "window": None}
+NCU_DRAM_BYTES_PER_STEP = {"atomic": 3_160_000_000,      # r1 launch list
+                           "window": 5_130_000_000}      # profiles/r2_launches_summary.txt: 0.206 GB read + 4.924 GB written (588 launches)
 # bytes each kernel itself must move per unit pixel (its own inputs + outputs, intermediates included)
 OWN_BYTES_PER_PX = {"window": {"prepass": 16.0, "splat": 44.0, "normalise": 40.0},       # K1: depth in, flow + z' out; K2: flow, z', RGB in, >= 1 slab cell out; K3: >= 1 slab cell in, 20 B out
                     "atomic": {"prepass": 4.0, "splat": 24.0, "normalise": 40.0}}
@@ -370,7 +371,10 @@ def run_ours(args):
                                "achieved_GBps": gbps(own[name], ms_, units_) if own.get(name) else None,
                                "frac": gbps(own[name], ms_, units_) / peak if own.get(name) else None}
         roofline = {"bound": "hbm", "kernel": kname, "achieved": step_gbps, "peak": peak, "unit": "GB/s",
-                    "frac": step_gbps / peak, "traffic": NCU_TRAFFIC_BYTES_PER_LAUNCH.get(args.accumulation),
+                    "frac": step_gbps / peak, "traffic": NCU_DRAM_BYTES_PER_STEP.get(args.accumulation),
+                    "traffic_what": "dram__bytes_read.sum + dram__bytes_write.sum of ALL launches of one step (ncu launch list under profiles/), "
+                                    "to be read against algorithmic_bytes_per_step",
+                    "kernel_alone_traffic_per_launch": NCU_TRAFFIC_BYTES_PER_LAUNCH.get(args.accumulation),
                     "peak_source": peak_src,
                     "what": "frac / achieved: 44 B x pixels of one step / device time of the whole timed step (all kernels, the timed "
                             "schedule); kernel_alone: each kernel on one stream in 24-unit launches against its OWN bytes per pixel "
