@@ -1,9 +1,7 @@
-# A/B of two builds of the library on the full 392-unit step (device-timed, default schedule) + the new GPU tests
+# A/B of every build of the library found next to the default one, on the full 392-unit step (device-timed, default schedule)
 TAG=${1:-r2_ab}
 O=gpurun_out/$TAG
 mkdir -p $O
-for lib in libtcwarp.so libtcwarp_alt.so; do
-  [ -f trajectorycrafter_b200/$lib ] || continue
-  TCW_LIB=$PWD/trajectorycrafter_b200/$lib timeout 200 python scripts/ncu_target.py 392 6 window 0 2>&1 | tail -2 | sed "s/^/$lib: /" | tee -a $O/ab.txt
+for lib in trajectorycrafter_b200/libtcwarp*.so; do
+  TCW_LIB=$PWD/$lib timeout 200 python scripts/ncu_target.py 392 6 window 0 2>&1 | tail -1 | sed "s|^|$(basename $lib): |" | tee -a $O/ab.txt
 done
-timeout 900 python -m pytest tests -x -q -m gpu > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -4 $O/pytest_gpu.log

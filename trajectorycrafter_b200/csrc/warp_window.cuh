@@ -357,6 +357,30 @@ __device__ __forceinline__ void win_step(const WinOut& o, int lane, bool on, int
     o.sw[p4] = s + w;
     __syncwarp();
 }
+// The top and the bottom cell of one column of one pixel in ONE step: both reads first, then both writes, so the two
+// shared-memory round trips overlap.  The caller guarantees that the two cells differ (a pixel that sits exactly on a cell row
+// has folded its bottom weight into the top one and sends the bottom to the scratch cell) and that no other lane addresses
+// either of them in this step.
+__device__ __forceinline__ void win_step2(const WinOut& o, int lane, bool onT, int idT, bool onB, int idB, u64 rg, u64 bz, float wT, float wB) {
+    const int cT = (onT && TCW_INRANGE(o.status, (unsigned)idT < (unsigned)o.scratch)) ? idT : o.scratch + lane;
+    const int cB = (onB && TCW_INRANGE(o.status, (unsigned)idB < (unsigned)o.scratch)) ? idB : o.scratch + lane;
+    const int pT = cT + (cT >> 3), pB = cB + (cB >> 3);
+    const float4 a = o.s4[pT], c = o.s4[pB];
+    const float sa = o.sw[pT], sc = o.sw[pB];
+    const u64 t2 = pk1(wT), b2 = pk1(wB);
+    float r, g, b, z;
+    if (cT == cB) {      // both switched off: the scratch cell takes one (meaningless) write
+        o.s4[pT] = a;
+    } else {
+        upk(fma2(rg, t2, pk(a.x, a.y)), r, g); upk(fma2(bz, t2, pk(a.z, a.w)), b, z);
+        o.s4[pT] = make_float4(r, g, b, z);
+        o.sw[pT] = sa + wT;
+        upk(fma2(rg, b2, pk(c.x, c.y)), r, g); upk(fma2(bz, b2, pk(c.z, c.w)), b, z);
+        o.s4[pB] = make_float4(r, g, b, z);
+        o.sw[pB] = sc + wB;
+    }
+    __syncwarp();
+}
 // live lanes form one run of consecutive lanes?
 __device__ __forceinline__ bool win_run(unsigned m) {
     if (m == 0u) return true;
@@ -484,20 +508,31 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
 
         int idNWA, idSWA, idNEA, idSEA, idNWB, idSWB, idNEB, idSEB;
         u64 wNW2, wSW2, wNE2, wSE2;
-        bool distinct = false;      // WM_SMEM: every step of this row addresses 32 different cells (or none)
-        if (!general) {
-            const bool dxA = oxA != fx0A, dxB = oxB != fx0B, dyA = oyA != fy0A, dyB = oyB != fy0B;   // ceil == floor + 1 ?
-            if (MODE == WM_SMEM) {
-                // Pixels A of all lanes are one step, pixels B another.  Two lanes of a step share a cell only if they
-                // share its column: with k = 2 ix0 + (ix1 - ix0), left and right columns both grow strictly from lane
-                // l-1 to lane l  <=>  k_l - k_{l-1} >= 2; live lanes must be one run so that neighbours are enough.
-                const unsigned mA = __ballot_sync(FULL, liveA), mB = __ballot_sync(FULL, liveB);
+        // WM_SMEM: can the row's (corner x pixel) steps run as plain read-modify-writes?  Pixels A of all lanes are one step,
+        // pixels B another.  Two lanes of a step share a cell only if they share its column: with k = 2 ix0 + (ix1 - ix0) of
+        // the UNCLAMPED floor, left and right columns both grow strictly from lane l-1 to lane l  <=>  k_l - k_{l-1} >= 2
+        // (clamping only moves columns into the pad ring, whose cells are never added); live lanes must be one run so that
+        // neighbours are enough.  dist 1: yes.  dist 2: yes when the even and the odd lanes go separately (columns grow from
+        // lane l-2 to lane l: images compressed to between a quarter and a half).  dist 0: the serialising routine.
+        const bool dxA = oxA != fx0A, dxB = oxB != fx0B, dyA = oyA != fy0A, dyB = oyB != fy0B;   // ceil == floor + 1 ?
+        int dist = 0;
+        if (MODE == WM_SMEM) {
+            const unsigned mA = __ballot_sync(FULL, liveA), mB = __ballot_sync(FULL, liveB);
+            if (win_run(mA) && win_run(mB)) {
                 const int kA = 2 * ix0A + (dxA ? 1 : 0), kB = 2 * ix0B + (dxB ? 1 : 0);
                 const int qA = __shfl_up_sync(FULL, kA, 1), qB = __shfl_up_sync(FULL, kB, 1);
                 const unsigned below = lane ? (1u << (lane - 1)) : 0u;
                 const bool bad = (liveA && (mA & below) && kA - qA < 2) || (liveB && (mB & below) && kB - qB < 2);
-                distinct = win_run(mA) && win_run(mB) && !__any_sync(FULL, bad);
+                if (!__any_sync(FULL, bad)) dist = 1;
+                else {
+                    const int rA = __shfl_up_sync(FULL, kA, 2), rB = __shfl_up_sync(FULL, kB, 2);
+                    const unsigned below2 = lane >= 2 ? (1u << (lane - 2)) : 0u;
+                    const bool bad2 = (liveA && (mA & below2) && kA - rA < 2) || (liveB && (mB & below2) && kB - rB < 2);
+                    if (!__any_sync(FULL, bad2)) dist = 2;
+                }
             }
+        }
+        if (!general) {
             const u64 fx02 = pk(fx0A, fx0B), fy02 = pk(fy0A, fy0B);
             const u64 fx12 = pk(dxA ? fx0A + 1.0f : fx0A, dxB ? fx0B + 1.0f : fx0B);
             const u64 fy12 = pk(dyA ? fy0A + 1.0f : fy0A, dyB ? fy0B + 1.0f : fy0B);
@@ -529,12 +564,24 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
         }
         float wNWA, wNWB, wSWA, wSWB, wNEA, wNEB, wSEA, wSEB;
         upk(wNW2, wNWA, wNWB); upk(wSW2, wSWA, wSWB); upk(wNE2, wNEA, wNEB); upk(wSE2, wSEA, wSEB);
-        if (MODE == WM_SMEM && distinct) {
-            // eight plain steps in a fixed order: NW, SW, NE, SE of the A pixels and of the B pixels
-            win_step(o, lane, liveA, idNWA, rgA, bzA, wNWA); win_step(o, lane, liveB, idNWB, rgB, bzB, wNWB);
-            win_step(o, lane, liveA, idSWA, rgA, bzA, wSWA); win_step(o, lane, liveB, idSWB, rgB, bzB, wSWB);
-            win_step(o, lane, liveA, idNEA, rgA, bzA, wNEA); win_step(o, lane, liveB, idNEB, rgB, bzB, wNEB);
-            win_step(o, lane, liveA, idSEA, rgA, bzA, wSEA); win_step(o, lane, liveB, idSEB, rgB, bzB, wSEB);
+        if (MODE == WM_SMEM && dist) {
+            // plain steps in a fixed order: NW, SW, NE, SE of the A pixels and of the B pixels (a negative id: pad ring or a
+            // pixel that adds nothing)
+            // top and bottom cell of a column go in one step; they are the same cell when the pixel sits exactly on a cell
+            // row (or the bottom one is a pad cell): then the top takes both weights and the bottom step is switched off
+            const bool tA = idSWA >= 0 && idSWA != idNWA, tB = idSWB >= 0 && idSWB != idNWB;
+            const bool uA = idSEA >= 0 && idSEA != idNEA, uB = idSEB >= 0 && idSEB != idNEB;
+            if (idSWA >= 0 && !tA) { wNWA += wSWA; }
+            if (idSWB >= 0 && !tB) { wNWB += wSWB; }
+            if (idSEA >= 0 && !uA) { wNEA += wSEA; }
+            if (idSEB >= 0 && !uB) { wNEB += wSEB; }
+            for (int par = 0; par < dist; ++par) {
+                const bool mine = dist == 1 || (lane & 1) == par;
+                win_step2(o, lane, mine && idNWA >= 0, idNWA, mine && tA, idSWA, rgA, bzA, wNWA, wSWA);
+                win_step2(o, lane, mine && idNWB >= 0, idNWB, mine && tB, idSWB, rgB, bzB, wNWB, wSWB);
+                win_step2(o, lane, mine && idNEA >= 0, idNEA, mine && uA, idSEA, rgA, bzA, wNEA, wSEA);
+                win_step2(o, lane, mine && idNEB >= 0, idNEB, mine && uB, idSEB, rgB, bzB, wNEB, wSEB);
+            }
             continue;
         }
 
@@ -594,7 +641,10 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
     }
 }
 
-__global__ void __launch_bounds__(WIN_WARPS * 32, 3)
+#ifndef TCW_WIN_MINB
+#define TCW_WIN_MINB 3
+#endif
+__global__ void __launch_bounds__(WIN_WARPS * 32, TCW_WIN_MINB)
 k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) unsigned char win_smem[];
