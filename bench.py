@@ -391,6 +391,28 @@ def run_ours(args):
                                          if NCU_DRAM_BYTES_PER_STEP.get(args.accumulation) else None),
                     "step_frac": step_gbps / peak}
 
+    # ---- the opt-in float-reduction mode on the same step, same timing (not the metric: its summation order is not fixed)
+    other_modes = None
+    if rank == 0 and world == 1 and not args.no_extras and args.accumulation == "window":
+        def atomic_step():
+            warper.forward_warp_matrices(frames_d, depths_d, M_d, src_index=src_d, per_frame_max=True, check_range=flag, out=out,
+                                         accumulation="atomic")
+        for _ in range(4):
+            atomic_step()
+        a0, a1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        a0.record()
+        for _ in range(args.steps):
+            atomic_step()
+        a1.record()
+        torch.cuda.synchronize()
+        a_ms = a0.elapsed_time(a1) / args.steps
+        other_modes = {"atomic": {"ms_per_step": a_ms, "Mpix_per_s": px_per_step / (a_ms * 1e-3) / 1e6,
+                                  "frac": ALGO_BYTES_PER_PX * px_per_step / (a_ms * 1e-3) / 1e9 / peak,
+                                  "what": ACCUMULATION["atomic"] + " -- Warper(..., accumulation='atomic') / TCW_ATOMIC_F32"}}
+        for _ in range(2):      # leave the default mode's graph and buffers as the later legs expect them
+            step()
+        torch.cuda.synchronize()
+
     # ---- the literal metric shape: ONE 49-unit trajectory (49x384x672, preset (0, 30)), inputs resident, device-timed
     clip49 = None
     if rank == 0 and not args.no_extras:
@@ -666,6 +688,8 @@ def run_ours(args):
             line["cpu_baseline_reference"] = cpu_ref
         if cpu_port is not None:
             line["cpu_baseline_port"] = cpu_port
+        if other_modes is not None:
+            line["other_modes"] = other_modes
         if clip49 is not None:
             line["clip49"] = clip49
         if dropin is not None:

@@ -381,7 +381,9 @@ static void win_layout(const tcw_ctx* ctx, int n_units, int h, int w, int flags,
     L->ns = L->strips_x * ((h + 7) / 8);
     L->nh = 2 * L->ns;
     L->ng = (L->nh + WIN_GROUP - 1) / WIN_GROUP;
-    L->pool_cells = (long long)WIN_POOL_MULT * (long long)hw + 4096;
+    // slab pool of a unit in flight: one WIN_CAP slot per (strip, pass) for the shared-memory windows, then WIN_POOL_MULT * h * w
+    // cells shared by the footprints that are too large for a window
+    L->pool_cells = (long long)L->ns * 2 * WIN_CAP + (long long)WIN_POOL_MULT * (long long)hw + 4096;
     size_t off = header_bytes(n_units);
     L->hdr = off;
     auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };

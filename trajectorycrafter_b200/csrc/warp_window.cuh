@@ -37,7 +37,10 @@ constexpr int WIN_SCRATCH = 32;                               // scratch cells b
 constexpr int WIN_P4 = (WIN_CAP + WIN_SCRATCH) + (WIN_CAP + WIN_SCRATCH) / 8 + 1;      // float4 slots: one pad slot per 8 cells (stride-2 lanes stay conflict-free)
 constexpr int WIN_PW = WIN_P4;                                // float slots: the weight plane uses the float4 plane's padded index
 constexpr int WIN_BYTES = ((WIN_P4 * 16 + WIN_PW * 4 + WIN_CAP) + 15) / 16 * 16;
-constexpr int WIN_WARPS = 4;                                 // warps (strips) per CTA of K2
+#ifndef TCW_WIN_WARPS
+#define TCW_WIN_WARPS 2
+#endif
+constexpr int WIN_WARPS = TCW_WIN_WARPS;                     // warps (strips) per CTA of K2
 constexpr int WIN_GROUP = 8;                                 // half-strips per K1 CTA = per box group
 constexpr int WIN_PRE_WARPS = WIN_GROUP / 2;                 // K1: one warp per 64 x 8 strip = two half-strips
 constexpr int WIN_POOL_MULT = 3;                             // slab pool of a unit: WIN_POOL_MULT * h * w cells
@@ -642,7 +645,7 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
 }
 
 #ifndef TCW_WIN_MINB
-#define TCW_WIN_MINB 3
+#define TCW_WIN_MINB (12 / TCW_WIN_WARPS)
 #endif
 __global__ void __launch_bounds__(WIN_WARPS * 32, TCW_WIN_MINB)
 k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
@@ -722,8 +725,14 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
             long long off = 0;
             bool shared_plane = false;
             if (cells > 0) {
-                if (lane == 0) off = (long long)atomicAdd(A.counter + sl, cells);
-                off = __shfl_sync(FULL, off, 0);
+                if (mode == WM_SMEM) {
+                    // a window's slab has a place of its own: slot 2 * strip + pass of WIN_CAP cells each -- no allocation, no atomic
+                    off = (long long)(2 * strip + p) * WIN_CAP;
+                } else {
+                    // larger footprints share the rest of the pool (one atomic per such footprint)
+                    if (lane == 0) off = (long long)A.ns * 2 * WIN_CAP + (long long)atomicAdd(A.counter + sl, cells);
+                    off = __shfl_sync(FULL, off, 0);
+                }
                 if (off + cells > A.pool_cells || off < 0) { shared_plane = true; mode = WM_GLOBAL; }      // pool exhausted (the counter may wrap for absurd inputs)
             }
             int idbase;
@@ -750,9 +759,21 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
                 splat_window_rows<WM_SMEM>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
                 __syncwarp();
                 // the window becomes a dense slab (cells in window order == slab order)
-                for (int i = lane; i < cells; i += 32) {
-                    __stcg(o.g4 + i, o.s4[i + (i >> 3)]);
-                    __stcg(o.gw + i, o.sw[i + (i >> 3)]);
+                // (four cells per lane and trip: the shared-memory reads of a trip are issued before its global stores)
+                for (int i0 = lane; i0 < cells; i0 += 128) {
+                    float4 v4[4];
+                    float vw[4];
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int i = i0 + 32 * k, j = i < cells ? i : lane;
+                        v4[k] = o.s4[j + (j >> 3)];
+                        vw[k] = o.sw[j + (j >> 3)];
+                    }
+                    #pragma unroll
+                    for (int k = 0; k < 4; ++k) {
+                        const int i = i0 + 32 * k;
+                        if (i < cells) { __stcg(o.g4 + i, v4[k]); __stcg(o.gw + i, vw[k]); }
+                    }
                 }
                 __syncwarp();
             } else {
@@ -839,8 +860,8 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
     for (int r = 0; r < 8; ++r) { acc[r] = make_float4(0.f, 0.f, 0.f, 0.f); accw[r] = 0.f; }
 
     // adds the n listed slabs (ascending half-strip order) to this warp's 32 x 8 cells.  Branch-free: a cell outside
-    // the slab reads the zero cell behind the pools, so all sixteen loads of a slab are in flight together and every
-    // accumulator takes the same sequence of additions (x + 0 changes nothing).
+    // the slab reads the zero cell behind the pools (an L1 hit), so all sixteen loads of a slab are in flight together and every
+    // accumulator takes the same sequence of additions (x + 0 changes nothing).  Predicated loads instead were slower (114 registers).
     const unsigned zero_cell = (unsigned)((long long)(A.n_slots - sl) * A.pool_cells);
     const char* __restrict__ b4 = (const char*)p4;
     const char* __restrict__ b1 = (const char*)pw;
@@ -857,8 +878,8 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
             #pragma unroll
             for (int r = 0; r < 8; ++r) {
                 const unsigned cu = ((unsigned)(r0 + r) < (unsigned)bh && colin && TCW_INRANGE(N.range_flag, (unsigned)ci < (unsigned)A.pool_cells)) ? (unsigned)ci : zero_cell;
-                s4[r] = __ldcg((const float4*)(b4 + (size_t)cu * 16u));
-                sw[r] = __ldcg((const float*)(b1 + (size_t)cu * 4u));
+                s4[r] = __ldg((const float4*)(b4 + (size_t)cu * 16u));       // written by an earlier kernel, read-only here: L1 keeps the
+                sw[r] = __ldg((const float*)(b1 + (size_t)cu * 4u));        // zero cell and the lines two rows share (ld.cg: 2.40 -> 1.48 ms)
                 ci += bw;
             }
             #pragma unroll
