@@ -43,7 +43,7 @@ constexpr int WIN_BYTES = ((WIN_P4 * 16 + WIN_PW * 4 + WIN_CAP) + 15) / 16 * 16;
 constexpr int WIN_WARPS = TCW_WIN_WARPS;                     // warps (strips) per CTA of K2
 constexpr int WIN_GROUP = 8;                                 // half-strips per K1 CTA = per box group
 constexpr int WIN_PRE_WARPS = WIN_GROUP / 2;                 // K1: one warp per 64 x 8 strip = two half-strips
-constexpr int WIN_POOL_MULT = 3;                             // slab pool of a unit: WIN_POOL_MULT * h * w cells
+constexpr int WIN_POOL_MULT = 6;                             // shared part of a unit's slab pool: WIN_POOL_MULT * h * w cells (rough depth maps need ~3: DESIGN.md section 5)
 constexpr int WIN_MAXC = 64;                                 // candidate slabs one K3 warp lists at a time
 
 struct WinBox { short x0, y0, bw, bh; int flags, pad; };     // cropped target coords; bw == 0: no cell.  flags bit 0: has pile pixels
