@@ -370,7 +370,7 @@ struct WinLayout {
     int NL, g2, S, P;                 // lanes, units per chunk, splat slots, prep slots
     int strips_x, ns, nh, ng;
     long long pool_cells;
-    size_t hdr, o_counter, o_flag, o_box, o_grp, o_z, o_flow, o_off, o_sbox, o_pile, o_pool4, o_poolw, o_spill4, o_spillw, o_tmp, total;
+    size_t hdr, o_counter, o_flag, o_box, o_grp, o_z, o_flow, o_sbox, o_pile, o_pool4, o_poolw, o_spill4, o_spillw, o_tmp, total;
 };
 static void win_layout(const tcw_ctx* ctx, int n_units, int h, int w, int flags, WinLayout* L) {
     const size_t hw = (size_t)h * w;
@@ -393,7 +393,6 @@ static void win_layout(const tcw_ctx* ctx, int n_units, int h, int w, int flags,
     L->o_grp = take((size_t)L->P * L->ng * sizeof(WinGrp));
     L->o_z = take((size_t)L->P * hw * sizeof(float));
     L->o_flow = take((size_t)L->P * 2 * hw * sizeof(float));
-    L->o_off = take((size_t)L->S * L->nh * sizeof(int));
     L->o_sbox = take((size_t)L->S * L->nh * sizeof(WinBox));
     L->o_pile = take((size_t)L->S * L->ns * 8 * sizeof(float));
     // each pool array is followed by 256 B of zeros: cell S * pool_cells is the "nothing here" cell of the branch-free gather
@@ -433,7 +432,7 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
     A.counter = (int*)(ws + L.o_counter); A.spill_flag = (int*)(ws + L.o_flag);
     A.box = (WinBox*)(ws + L.o_box); A.grp = (WinGrp*)(ws + L.o_grp);
     A.zbuf = (float*)(ws + L.o_z); A.flowbuf = (float*)(ws + L.o_flow);
-    A.slab_off = (int*)(ws + L.o_off); A.sbox = (WinBox*)(ws + L.o_sbox); A.pile = (float*)(ws + L.o_pile);
+    A.sbox = (WinBox*)(ws + L.o_sbox); A.pile = (float*)(ws + L.o_pile);
     A.pool4 = (float4*)(ws + L.o_pool4); A.poolw = (float*)(ws + L.o_poolw); A.pool_cells = L.pool_cells; A.n_slots = L.S;
     A.spill4 = (float4*)(ws + L.o_spill4); A.spillw = (float*)(ws + L.o_spillw);
     A.status = J.range_flag;

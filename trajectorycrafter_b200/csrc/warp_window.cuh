@@ -61,7 +61,7 @@ struct WinArgs {
     float* flow_out;                                         // (n,2,h,w) caller's flow12, or nullptr -> flowbuf
     float* flowbuf; float* zbuf; WinBox* box; WinGrp* grp;   // per prep slot
     // K2 products
-    int* counter; int* spill_flag; int* slab_off; float* pile;   // per splat slot
+    int* counter; int* spill_flag; float* pile;                  // per splat slot
     WinBox* sbox;                                            // per splat slot: the slabs K2 actually wrote (box + offset in `pad`; bw == 0: none)
     float4* pool4; float* poolw; long long pool_cells; int n_slots;
     float4* spill4; float* spillw;
@@ -687,7 +687,6 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
 
     const WinBox b0 = A.box[(size_t)ps * A.nh + hs0], b1 = A.box[(size_t)ps * A.nh + hs0 + 1];
     const int a0 = (int)b0.bw * b0.bh, a1 = (int)b1.bw * b1.bh;
-    int* offp = A.slab_off + (size_t)sl * A.nh + hs0;
     float* pilep = A.pile + ((size_t)sl * A.ns + strip) * 8;
     u64 hrg = 0, hbz = 0;
     float hwt = 0.f;
@@ -802,7 +801,6 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
         r.pad = off;
         A.sbox[(size_t)sl * A.nh + hs0 + lane] = r;
     }
-    if (lane == 0) { offp[0] = off0; offp[1] = off1; }
     // pixels that sat exactly on padded cell (2,2): one sum per strip, added by K3 to output pixel (1,1)
     float hr = 0.f, hg = 0.f, hb = 0.f, hz = 0.f;
     const bool anyp = __any_sync(FULL, any_pile);
