@@ -150,8 +150,16 @@ int tcw_resize_pack(tcw_ctx* ctx, const float* frame, const float* mask, int n, 
  *                          (point_size 0 = render_pointcloud_zbuffer_vectorized :445-519: one pixel, clamped into the image),
  *                          nearest entry per pixel (64-bit atomicMin on depth bits | reversed entry index: bit-reproducible);
  *                          out_frame (3,h,w) with -1 in empty pixels, out_mask (h,w), out_depth (h,w)|NULL; workspace >= h*w*8 B
+ * tcw_pc_render_zbuffer_first   render_pointcloud_zbuffer_vectorized_fixed (:650-765), the sequential loop with a strict `<`:
+ *                          among equal depths the FIRST entry stays (depth bits | entry index); point_size <= 1 = one pixel,
+ *                          clamped into the image; same arguments and workspace
  * tcw_pc_render_bilinear   render_from_camera(use_bilinear=True) (:158-256, :351-443), one camera: depth-weighted bilinear
  *                          scatter (float reductions: tolerance parity); weights (N) DEVICE; workspace >= 256 + h*w*16 B
+ * tcw_pc_render_disc       render_from_camera(use_bilinear=False) = _splat_points_to_image_with_size (:258-349), one camera:
+ *                          every visible point stamped at round(pixel + offset) for the n_splats (<= 128) offsets of the disc,
+ *                          weight = point weight * exp(-2 depth / (max depth + 1e-8)) * splat_weights[j]; offsets_xy
+ *                          (n_splats x 2 ints: dx, dy) and splat_weights are HOST arrays built as the reference builds them;
+ *                          pixels with summed weight <= 1e-6 stay 0; workspace >= 256 + h*w*16 B
  */
 int tcw_pc_lift(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth, const float* Minv,
                 int b, int h, int w, int step, float* out_points, float* out_colors, void* cuda_stream);
@@ -159,9 +167,17 @@ int tcw_pc_render_zbuffer(tcw_ctx* ctx, const float* points, const float* colors
                           long long n_points, int h, int w, int point_size,
                           float* out_frame, float* out_mask, float* out_depth,
                           void* workspace, size_t workspace_bytes, void* cuda_stream);
+int tcw_pc_render_zbuffer_first(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                                long long n_points, int h, int w, int point_size,
+                                float* out_frame, float* out_mask, float* out_depth,
+                                void* workspace, size_t workspace_bytes, void* cuda_stream);
 int tcw_pc_render_bilinear(tcw_ctx* ctx, const float* points, const float* colors, const float* weights, const float* camera,
                            long long n_points, int h, int w, float depth_threshold,
                            float* out_frame, float* out_mask, void* workspace, size_t workspace_bytes, void* cuda_stream);
+int tcw_pc_render_disc(tcw_ctx* ctx, const float* points, const float* colors, const float* weights, const float* camera,
+                       long long n_points, int h, int w, float depth_threshold,
+                       const int* offsets_xy, const float* splat_weights, int n_splats,
+                       float* out_frame, float* out_mask, void* workspace, size_t workspace_bytes, void* cuda_stream);
 
 /*
  * The step right before the warp, on the device (reference models/infer.py:79-92, the numpy / torch lines that end

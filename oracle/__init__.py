@@ -222,9 +222,11 @@ def pc_lift(frame, mask1, depth, T1inv, K1inv, step=1):
     return pts, cols
 
 
-def pc_zbuffer(points, colors, T, K, h, w, point_size=1, clamp=False):
+def pc_zbuffer(points, colors, T, K, h, w, point_size=1, clamp=False, first_wins=False):
     """render_pointcloud_zbuffer_vectorized_point_size (:522-646) / render_pointcloud_zbuffer_vectorized (:445-519, clamp=True).
     Nearest entry per pixel; among equal depths the LAST entry in (point, offset) order (the sequential CPU index_put).
+    first_wins=True: render_pointcloud_zbuffer_vectorized_fixed (:650-765), whose loop `if depth < buffer` keeps the FIRST of
+    equal depths (and which clamps for point_size <= 1: pass clamp=True).
     Returns frame (1,3,h,w) with -1 in empty pixels, mask (1,1,h,w), depth (1,1,h,w)."""
     colors = np.asarray(colors, np.float32)
     cam, _, px, py = pc_project(points, T, K)
@@ -253,7 +255,7 @@ def pc_zbuffer(points, colors, T, K, h, w, point_size=1, clamp=False):
         end = np.append(start[1:], lin.size)
         for s0, e0 in zip(start, end):
             k = s0
-            while k + 1 < e0 and ez[k + 1] == ez[s0]:
+            while not first_wins and k + 1 < e0 and ez[k + 1] == ez[s0]:
                 k += 1
             frame[:, lin[s0]] = colors[ep[k]]
             dbuf[lin[s0]] = ez[s0]
@@ -289,3 +291,45 @@ def pc_bilinear(points, colors, weights, T, K, h, w, depth_threshold=100000.0):
         out[:, v] = (out[:, v] / wb[v]).astype(np.float32)
         return out.reshape(3, h, w), v.astype(np.float32).reshape(1, h, w)
     return out.reshape(3, h, w), wb.reshape(1, h, w)
+
+
+def pc_disc_table(point_size):
+    """The stamp of _splat_points_to_image_with_size (:281-296): offsets (dx, dy) and float32 Gaussian falloff weights."""
+    radius = int(point_size / 2)
+    offs, fall = [], []
+    for dy in range(-radius, radius + 1):
+        for dx in range(-radius, radius + 1):
+            dist = (dx ** 2 + dy ** 2) ** 0.5
+            if dist <= point_size / 2:
+                offs.append((dx, dy))
+                fall.append(np.exp(np.float32(-dist ** 2 / (2 * (point_size / 4) ** 2))))
+    return offs, np.asarray(fall, np.float32)
+
+
+def pc_disc(points, colors, weights, T, K, h, w, point_size=2.0, depth_threshold=100000.0):
+    """render_from_camera(use_bilinear=False) for one camera (:199-256) + _splat_points_to_image_with_size (:258-349):
+    sequential float32 scatter in the reference's order (point-major, offsets inside).  Returns (3,h,w), (1,h,w)."""
+    colors, weights = np.asarray(colors, np.float32), np.asarray(weights, np.float32).reshape(-1)
+    cam, proj, px, py = pc_project(points, T, K)
+    vis = (cam[2] > np.float32(0.1)) & (cam[2] < np.float32(depth_threshold)) & (px >= 0) & (px < w) & (py >= 0) & (py < h)
+    out = np.zeros((3, h * w), np.float32)
+    wb = np.zeros(h * w, np.float32)
+    if not vis.any():
+        return out.reshape(3, h, w), wb.reshape(1, h, w)
+    x, y, d, c, wt = px[vis], py[vis], proj[2][vis], colors[vis], weights[vis]
+    nd = (d / np.float32(d.max() + np.float32(1e-8))).astype(np.float32)
+    tw = (wt * np.exp((-nd * np.float32(2)).astype(np.float32)).astype(np.float32)).astype(np.float32)
+    offs, fall = pc_disc_table(point_size)
+    ex = np.stack([np.rint((x + np.float32(dx)).astype(np.float32)) for dx, _ in offs], 1).astype(np.int64)
+    ey = np.stack([np.rint((y + np.float32(dy)).astype(np.float32)) for _, dy in offs], 1).astype(np.int64)
+    fw = (tw[:, None] * fall[None, :]).astype(np.float32)
+    inb = (ex >= 0) & (ex < w) & (ey >= 0) & (ey < h)
+    lin = (ey * w + ex)[inb]
+    fwv = fw[inb]
+    cc = np.repeat(c[:, None, :], len(offs), 1)[inb]
+    for ch in range(3):
+        np.add.at(out[ch], lin, (cc[:, ch] * fwv).astype(np.float32))
+    np.add.at(wb, lin, fwv)
+    v = wb > np.float32(1e-6)
+    out[:, v] = (out[:, v] / wb[v]).astype(np.float32)
+    return out.reshape(3, h, w), v.astype(np.float32).reshape(1, h, w)

@@ -71,8 +71,9 @@ def main():
     p1, c1, w1 = pc.create_pointcloud_from_image(frame[1:], mask[1:], depth[1:], T1[1:], K[1:], 0.5)
     P, C, Wt = pc.merge_pointclouds([p0, p1], [c0, c1], [w0, w1])
     # exact ties for the z-buffer: a few duplicated points with other colours at the END of the cloud
-    dup = P[100:110].clone()
-    P = torch.cat([P, dup]); C = torch.cat([C, -C[100:110]]); Wt = torch.cat([Wt, Wt[100:110]])
+    pick = torch.arange(500, 9000, 212)             # spread over both images: most are visible from both target cameras
+    dup = P[pick].clone()
+    P = torch.cat([P, dup]); C = torch.cat([C, -C[pick]]); Wt = torch.cat([Wt, Wt[pick]])
     Tt = torch.stack([rot_y(-0.15), rot_y(0.25)])
     Tt[0, :3, 3] = torch.tensor([-0.3, 0.05, 0.4]); Tt[1, :3, 3] = torch.tensor([0.5, 0.0, -0.2])
     Kt = torch.tensor([[90.0, 0, 50.0], [0, 90.0, 28.0], [0, 0, 1]]).repeat(2, 1, 1)
@@ -85,6 +86,15 @@ def main():
         out[f"zbc/cam{cam}/frame"], out[f"zbc/cam{cam}/mask"] = f.numpy(), m.numpy()
     f, m = pc.render_from_camera(P, C, Wt, Tt, Kt, h, w)
     out["bil/frame"], out["bil/mask"] = f.numpy(), m.numpy()
+    # the disc splat of render_from_camera (use_bilinear=False) and the sequential "fixed" z-buffer (a Python loop over every
+    # footprint entry in the reference: seconds at this size)
+    for ps in (2.0, 3.0, 5.0):
+        f, m = pc.render_from_camera(P, C, Wt, Tt, Kt, h, w, point_size=ps, use_bilinear=False)
+        out[f"disc/ps{ps:g}/frame"], out[f"disc/ps{ps:g}/mask"] = f.numpy(), m.numpy()
+    for cam in range(2):
+        for ps in (1, 2, 3):
+            f, m = pc.render_pointcloud_zbuffer_vectorized_fixed(P, C, Tt[cam:cam + 1], Kt[cam:cam + 1], (h, w), ps)
+            out[f"zbf/cam{cam}_ps{ps}/frame"], out[f"zbf/cam{cam}_ps{ps}/mask"] = f.numpy(), m.numpy()
     print("cloud", tuple(P.shape), "zbuffer coverage", float(out["zb/cam0_ps1/mask"].mean()), float(out["zb/cam0_ps3/mask"].mean()),
           "bilinear coverage", float(m.mean()))
     path = os.path.join(ROOT, "tests", "golden", "pointcloud_cases.npz")

@@ -42,6 +42,24 @@ def test_oracle_renderers(z, cam):
     f, m = oracle.pc_bilinear(P, C, Wt, z["Tt"][cam], z["Kt"][cam], H, W)
     assert np.array_equal(m[None], z["bil/mask"][cam:cam + 1])
     assert np.abs(f - z["bil/frame"][cam]).max() <= BIL_TOL
+    for ps in (1, 2, 3):
+        f, m, _ = oracle.pc_zbuffer(P, C, z["Tt"][cam], z["Kt"][cam], H, W, ps, clamp=ps <= 1, first_wins=True)
+        assert np.array_equal(f, z[f"zbf/cam{cam}_ps{ps}/frame"]), "sequential z-buffer: the first of equal depths stays"
+        assert np.array_equal(m, z[f"zbf/cam{cam}_ps{ps}/mask"])
+    for ps in (2.0, 3.0, 5.0):
+        f, m = oracle.pc_disc(P, C, Wt, z["Tt"][cam], z["Kt"][cam], H, W, ps)
+        assert np.array_equal(m[None], z[f"disc/ps{ps:g}/mask"][cam:cam + 1])
+        assert np.abs(f - z[f"disc/ps{ps:g}/frame"][cam]).max() <= BIL_TOL
+
+
+def test_first_and_last_winner_rules_differ_on_the_duplicated_points(z):
+    """The fixture ends with duplicated points in other colours: the two z-buffer rules (last / first of equal depths) must
+    disagree in some pixels and nowhere in the mask."""
+    for cam in (0, 1):
+        for ps in (2, 3):
+            last, first = z[f"zb/cam{cam}_ps{ps}/frame"], z[f"zbf/cam{cam}_ps{ps}/frame"]
+            assert (last != first).any(axis=1).sum() >= 10
+            assert np.array_equal(z[f"zb/cam{cam}_ps{ps}/mask"], z[f"zbf/cam{cam}_ps{ps}/mask"])
 
 
 # ---------------------------------------------------------------------------------------------
@@ -88,6 +106,31 @@ def test_gpu_render_from_camera(pcw, z):
     assert err <= BIL_TOL
     e0, e1 = pcw.render_from_camera(None, None, None, T(z["Tt"]), T(z["Kt"]), H, W)
     assert e0.shape == (2, 3, H, W) and float(e0.abs().max()) == 0.0 and float(e1.max()) == 0.0
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("cam", [0, 1])
+def test_gpu_zbuffer_fixed_bit_exact(pcw, z, cam):
+    P, C = T(z["cloud/points"]), T(z["cloud/colors"])
+    Tt, Kt = T(z["Tt"][cam:cam + 1]), T(z["Kt"][cam:cam + 1])
+    for ps in (1, 2, 3):
+        f, m = pcw.render_pointcloud_zbuffer_vectorized_fixed(P, C, Tt, Kt, (H, W), ps)
+        assert np.array_equal(f.cpu().numpy(), z[f"zbf/cam{cam}_ps{ps}/frame"]), f"point_size {ps}: first-of-equal winners must be bit-exact"
+        assert np.array_equal(m.cpu().numpy(), z[f"zbf/cam{cam}_ps{ps}/mask"])
+
+
+@pytest.mark.gpu
+def test_gpu_render_from_camera_disc(pcw, z):
+    for ps in (2.0, 3.0, 5.0):
+        f, m = pcw.render_from_camera(T(z["cloud/points"]), T(z["cloud/colors"]), T(z["cloud/weights"]), T(z["Tt"]), T(z["Kt"]), H, W,
+                                      point_size=ps, use_bilinear=False)
+        assert np.array_equal(m.cpu().numpy(), z[f"disc/ps{ps:g}/mask"]), "coverage mask must be bit-exact"
+        err = np.abs(f.cpu().numpy() - z[f"disc/ps{ps:g}/frame"]).max()
+        print(f"render_from_camera(use_bilinear=False, point_size={ps:g}): colour max |d| {err:.2e}")
+        assert err <= BIL_TOL
+    with pytest.raises(RuntimeError):
+        pcw.render_from_camera(T(z["cloud/points"]), T(z["cloud/colors"]), T(z["cloud/weights"]), T(z["Tt"]), T(z["Kt"]), H, W,
+                               point_size=30.0, use_bilinear=False)          # 709 offsets: more than the table holds
 
 
 @pytest.mark.gpu

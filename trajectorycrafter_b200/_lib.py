@@ -45,6 +45,8 @@ SIGNATURES = {
     "tcw_resize_pack": (c_int, [c_void_p, _FP, _FP, c_int, c_int, c_int, c_int, c_int, _FP, _FP, c_void_p]),
     "tcw_pc_lift": (c_int, [c_void_p, _FP, _FP, _FP, _FP, c_int, c_int, c_int, c_int, _FP, _FP, c_void_p]),
     "tcw_pc_render_zbuffer": (c_int, [c_void_p, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_int, _FP, _FP, _FP, _VP, c_size_t, c_void_p]),
+    "tcw_pc_render_zbuffer_first": (c_int, [c_void_p, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_int, _FP, _FP, _FP, _VP, c_size_t, c_void_p]),
+    "tcw_pc_render_disc": (c_int, [c_void_p, _FP, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_float, POINTER(c_int), POINTER(c_float), c_int, _FP, _FP, _VP, c_size_t, c_void_p]),
     "tcw_pc_render_bilinear": (c_int, [c_void_p, _FP, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_float, _FP, _FP, _VP, c_size_t, c_void_p]),
     "tcw_depth_post": (c_int, [c_void_p, _FP, c_int, c_int, c_int, c_int, c_float, c_float, c_float, _FP, _FP, c_void_p]),
     "tcw_ipc_alloc": (c_int, [c_void_p, c_size_t, POINTER(c_void_p), c_void_p]),

@@ -6,6 +6,8 @@
 //                   its point_size x point_size footprint, keep the nearest entry per pixel
 //   k_pc_resolve    second half: winner -> colour / mask / depth
 //   k_pc_range, k_pc_bilinear, k_pc_normalise      render_from_camera :158-256 + _splat_points_bilinear_efficient :351-443
+//   k_pc_disc       render_from_camera(use_bilinear=False): _splat_points_to_image_with_size :258-349
+//   (k_pc_zbuffer with first_wins: render_pointcloud_zbuffer_vectorized_fixed :650-765)
 //
 // Arithmetic.  The reference's per-pixel products are broadcast matmuls of (3x3)(3x1) / (4x4)(4x1) blocks: sequential un-fused
 // fp32 like the main path (models/utils.py:388-399).  Its per-POINT products are plain GEMMs `T @ points.T` (4 x N) and
@@ -64,8 +66,9 @@ constexpr unsigned long long PC_EMPTY = 0xffffffffffffffffull;
 
 __global__ void __launch_bounds__(256)
 k_pc_zbuffer(const float* __restrict__ points, PcCamera C, long long n_points, int h, int w, int point_size,
-             unsigned long long* __restrict__ zbuf) {
-    // point_size 0: the single-pixel variant render_pointcloud_zbuffer_vectorized (:445-519), which CLAMPS the rounded pixel
+             int first_wins, unsigned long long* __restrict__ zbuf) {
+    // first_wins: render_pointcloud_zbuffer_vectorized_fixed (:650-765), a sequential loop with a strict `<`: among equal depths
+    // the FIRST entry stays.  point_size 0: the single-pixel variant render_pointcloud_zbuffer_vectorized (:445-519), which CLAMPS the rounded pixel
     // into the image (:483-484) instead of dropping it
     const bool clamp_mode = point_size == 0;
     const int radius = point_size / 2, side = 2 * radius + 1, n_splats = side * side;
@@ -84,7 +87,7 @@ k_pc_zbuffer(const float* __restrict__ points, PcCamera C, long long n_points, i
                 if (clamp_mode) { xr = fminf(fmaxf(xr, 0.0f), wf - 1.0f); yr = fminf(fmaxf(yr, 0.0f), hf - 1.0f); }
                 if (!(xr >= 0.0f && xr < wf && yr >= 0.0f && yr < hf)) continue;
                 const unsigned entry = (unsigned)(i * n_splats + j);
-                atomicMin(zbuf + (size_t)((int)yr) * w + (int)xr, hi | (unsigned long long)(0xffffffffu - entry));
+                atomicMin(zbuf + (size_t)((int)yr) * w + (int)xr, hi | (unsigned long long)(first_wins ? entry : 0xffffffffu - entry));
             }
         }
     }
@@ -92,14 +95,15 @@ k_pc_zbuffer(const float* __restrict__ points, PcCamera C, long long n_points, i
 
 // :622-641: colour of the winner (empty pixels -1), mask = depth > 0, depth buffer (empty 0)
 __global__ void __launch_bounds__(256)
-k_pc_resolve(const unsigned long long* __restrict__ zbuf, const float* __restrict__ colors, int hw, int n_splats,
+k_pc_resolve(const unsigned long long* __restrict__ zbuf, const float* __restrict__ colors, int hw, int n_splats, int first_wins,
              float* __restrict__ out_frame, float* __restrict__ out_mask, float* __restrict__ out_depth) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= hw) return;
     const unsigned long long k = zbuf[p];
     float r = -1.0f, g = -1.0f, b = -1.0f, d = 0.0f;
     if (k != PC_EMPTY) {
-        const unsigned entry = 0xffffffffu - (unsigned)(k & 0xffffffffull);
+        const unsigned low = (unsigned)(k & 0xffffffffull);
+        const unsigned entry = first_wins ? low : 0xffffffffu - low;
         const float* c = colors + (size_t)(entry / (unsigned)n_splats) * 3;
         r = c[0]; g = c[1]; b = c[2];
         d = __uint_as_float((unsigned)(k >> 32));
@@ -171,13 +175,44 @@ k_pc_bilinear(const float* __restrict__ points, const float* __restrict__ colors
     }
 }
 
-// :433-441: colour = sum / weight where weight > 1e-8 (else the zero the buffer started with), mask = that test
+// ---- render_from_camera with use_bilinear=False: _splat_points_to_image_with_size (:258-349).  Every visible point is
+// stamped at round(pixel + offset) for the offsets of a disc of diameter point_size, with weight
+// point weight * exp(-2 * depth / (max depth + 1e-8)) * Gaussian falloff; the disc's offsets and falloff weights are built on
+// the host exactly as the reference builds them (Python double arithmetic, then float32 exp) and arrive as a table.
+struct PcDisc { int n; signed char dx[128]; signed char dy[128]; float w[128]; };
+
 __global__ void __launch_bounds__(256)
-k_pc_normalise(const float4* __restrict__ acc, int hw, float* __restrict__ out_frame, float* __restrict__ out_mask) {
+k_pc_disc(const float* __restrict__ points, const float* __restrict__ colors, const float* __restrict__ weights,
+          PcCamera C, PcDisc D, long long n_points, int h, int w, float depth_threshold, const unsigned* __restrict__ mm,
+          float4* __restrict__ acc) {
+    const float wf = (float)w, hf = (float)h;
+    if (mm[2] == 0u) return;
+    const float denom = __fadd_rn(dp_decode(mm[1]), 1e-8f);                                  // :277 depths.max() + 1e-8
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_points; i += (long long)gridDim.x * blockDim.x) {
+        float px, py, pz;
+        if (!pc_visible(C, points + i * 3, depth_threshold, wf, hf, px, py, pz)) continue;
+        const float nd = __fdiv_rn(pz, denom);
+        const float tw = __fmul_rn(weights[i], expf(__fmul_rn(-nd, 2.0f)));                   // :278-279
+        const float r = colors[i * 3], g = colors[i * 3 + 1], b = colors[i * 3 + 2];
+        for (int j = 0; j < D.n; ++j) {
+            const float xr = rintf(__fadd_rn(px, (float)D.dx[j])), yr = rintf(__fadd_rn(py, (float)D.dy[j]));   // :302, :315
+            if (!(xr >= 0.0f && xr < wf && yr >= 0.0f && yr < hf)) continue;
+            const float fw = __fmul_rn(tw, D.w[j]);                                           // :312
+            float4* a = acc + (size_t)((int)yr) * w + (int)xr;
+            asm volatile("red.global.add.v4.f32 [%0], {%1, %2, %3, %4};"
+                         :: "l"(a), "f"(__fmul_rn(r, fw)), "f"(__fmul_rn(g, fw)), "f"(__fmul_rn(b, fw)), "f"(fw) : "memory");
+        }
+    }
+}
+
+// :433-441 / :343-347: colour = sum / weight where weight > threshold (1e-8 bilinear, 1e-6 disc; else the zero the buffer
+// started with), mask = that test
+__global__ void __launch_bounds__(256)
+k_pc_normalise(const float4* __restrict__ acc, int hw, float threshold, float* __restrict__ out_frame, float* __restrict__ out_mask) {
     const int p = blockIdx.x * blockDim.x + threadIdx.x;
     if (p >= hw) return;
     const float4 a = acc[p];
-    const bool v = a.w > 1e-8f;
+    const bool v = a.w > threshold;
     out_frame[p] = v ? __fdiv_rn(a.x, a.w) : 0.0f;
     out_frame[hw + p] = v ? __fdiv_rn(a.y, a.w) : 0.0f;
     out_frame[2 * hw + p] = v ? __fdiv_rn(a.z, a.w) : 0.0f;

@@ -782,10 +782,10 @@ static int pc_grid(const tcw_ctx* ctx, long long n) {
     return (int)(want < cap ? (want > 0 ? want : 1) : cap);
 }
 
-TCW_API int tcw_pc_render_zbuffer(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
-                                  long long n_points, int h, int w, int point_size,
-                                  float* out_frame, float* out_mask, float* out_depth,
-                                  void* workspace, size_t workspace_bytes, void* cuda_stream) {
+static int pc_zbuffer_impl(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                           long long n_points, int h, int w, int point_size, int first_wins,
+                           float* out_frame, float* out_mask, float* out_depth,
+                           void* workspace, size_t workspace_bytes, void* cuda_stream) {
     if (!ctx || !camera || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer: NULL argument");
     if (n_points < 0 || (n_points > 0 && (!points || !colors)) || h <= 0 || w <= 0 || point_size < 0 || point_size > 64)
         return fail(TCW_E_ARG, "tcw_pc_render_zbuffer: bad argument");
@@ -801,12 +801,29 @@ TCW_API int tcw_pc_render_zbuffer(tcw_ctx* ctx, const float* points, const float
     unsigned long long* zbuf = (unsigned long long*)workspace;
     CUDA_TRY(cudaMemsetAsync(zbuf, 0xff, hw * sizeof(unsigned long long), st));
     if (n_points > 0) {
-        k_pc_zbuffer<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, C, n_points, h, w, point_size, zbuf);
+        k_pc_zbuffer<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, C, n_points, h, w, point_size, first_wins, zbuf);
         LAUNCH_CHECK("k_pc_zbuffer");
     }
-    k_pc_resolve<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(zbuf, colors, (int)hw, n_splats, out_frame, out_mask, out_depth);
+    k_pc_resolve<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(zbuf, colors, (int)hw, n_splats, first_wins, out_frame, out_mask, out_depth);
     LAUNCH_CHECK("k_pc_resolve");
     return TCW_OK;
+}
+
+TCW_API int tcw_pc_render_zbuffer(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                                  long long n_points, int h, int w, int point_size,
+                                  float* out_frame, float* out_mask, float* out_depth,
+                                  void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    return pc_zbuffer_impl(ctx, points, colors, camera, n_points, h, w, point_size, 0, out_frame, out_mask, out_depth,
+                           workspace, workspace_bytes, cuda_stream);
+}
+
+// render_pointcloud_zbuffer_vectorized_fixed (:650-765): among equal depths the FIRST entry stays; point_size <= 1 clamps
+TCW_API int tcw_pc_render_zbuffer_first(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                                        long long n_points, int h, int w, int point_size,
+                                        float* out_frame, float* out_mask, float* out_depth,
+                                        void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    return pc_zbuffer_impl(ctx, points, colors, camera, n_points, h, w, point_size <= 1 ? 0 : point_size, 1, out_frame, out_mask,
+                           out_depth, workspace, workspace_bytes, cuda_stream);
 }
 
 TCW_API int tcw_pc_render_bilinear(tcw_ctx* ctx, const float* points, const float* colors, const float* weights, const float* camera,
@@ -832,7 +849,46 @@ TCW_API int tcw_pc_render_bilinear(tcw_ctx* ctx, const float* points, const floa
         k_pc_bilinear<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, colors, weights, C, n_points, h, w, depth_threshold, mm, acc);
         LAUNCH_CHECK("k_pc_bilinear");
     }
-    k_pc_normalise<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(acc, (int)hw, out_frame, out_mask);
+    k_pc_normalise<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(acc, (int)hw, 1e-8f, out_frame, out_mask);
+    LAUNCH_CHECK("k_pc_normalise");
+    return TCW_OK;
+}
+
+// render_from_camera(use_bilinear=False) for one camera: disc stamps with Gaussian falloff (:258-349)
+TCW_API int tcw_pc_render_disc(tcw_ctx* ctx, const float* points, const float* colors, const float* weights, const float* camera,
+                               long long n_points, int h, int w, float depth_threshold,
+                               const int* offsets_xy, const float* splat_weights, int n_splats,
+                               float* out_frame, float* out_mask, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    if (!ctx || !camera || !out_frame || !out_mask || !offsets_xy || !splat_weights) return fail(TCW_E_ARG, "tcw_pc_render_disc: NULL argument");
+    if (n_points < 0 || (n_points > 0 && (!points || !colors || !weights)) || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_pc_render_disc: bad argument");
+    if (n_splats < 1 || n_splats > 128) return fail(TCW_E_ARG, "tcw_pc_render_disc: 1..128 disc offsets (point_size < 12)");
+    const size_t hw = (size_t)h * w;
+    if (hw >= 0x7fffffffull) return fail(TCW_E_ARG, "tcw_pc_render_disc: image too large");
+    if (!workspace || workspace_bytes < 256 + hw * sizeof(float4)) return fail(TCW_E_WORKSPACE, "tcw_pc_render_disc: workspace needs 256 + h*w*16 bytes");
+    cudaStream_t st = (cudaStream_t)cuda_stream;
+    PcCamera C;
+    memcpy(C.T, camera, sizeof(C.T));
+    memcpy(C.K, camera + 12, sizeof(C.K));
+    PcDisc D;
+    memset(&D, 0, sizeof(D));
+    D.n = n_splats;
+    for (int j = 0; j < n_splats; ++j) {
+        const int dx = offsets_xy[2 * j], dy = offsets_xy[2 * j + 1];
+        if (dx < -127 || dx > 127 || dy < -127 || dy > 127) return fail(TCW_E_ARG, "tcw_pc_render_disc: offset out of range");
+        D.dx[j] = (signed char)dx; D.dy[j] = (signed char)dy; D.w[j] = splat_weights[j];
+    }
+    unsigned* mm = (unsigned*)workspace;
+    float4* acc = (float4*)((char*)workspace + 256);
+    CUDA_TRY(cudaMemsetAsync(mm, 0xff, sizeof(unsigned), st));
+    CUDA_TRY(cudaMemsetAsync(mm + 1, 0, 2 * sizeof(unsigned), st));
+    CUDA_TRY(cudaMemsetAsync(acc, 0, hw * sizeof(float4), st));
+    if (n_points > 0) {
+        k_pc_range<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, C, n_points, h, w, depth_threshold, mm);
+        LAUNCH_CHECK("k_pc_range");
+        k_pc_disc<<<pc_grid(ctx, n_points), 256, 0, st>>>(points, colors, weights, C, D, n_points, h, w, depth_threshold, mm, acc);
+        LAUNCH_CHECK("k_pc_disc");
+    }
+    k_pc_normalise<<<(unsigned)((hw + 255) / 256), 256, 0, st>>>(acc, (int)hw, 1e-6f, out_frame, out_mask);
     LAUNCH_CHECK("k_pc_normalise");
     return TCW_OK;
 }

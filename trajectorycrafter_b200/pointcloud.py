@@ -2,9 +2,8 @@
 libtcwarp.so.  Same method names, argument order and return shapes; tensors live on the CUDA device.
 No CPU path: a missing library raises (``_lib.load``).
 
-Built: ``lift_to_3d_pointcloud`` / ``create_pointcloud_from_image`` / ``merge_pointclouds`` / ``downsample_pointcloud``,
-``render_from_camera`` (the default ``use_bilinear=True`` branch) and the two z-buffer renderers.  Not built: the
-``use_bilinear=False`` square splat of ``render_from_camera`` (:258-349) and ``render_pointcloud_zbuffer_vectorized_fixed``.
+Built: every method of the class -- ``lift_to_3d_pointcloud`` / ``create_pointcloud_from_image`` / ``merge_pointclouds`` /
+``downsample_pointcloud``, ``render_from_camera`` (bilinear and disc splats) and the three z-buffer renderers.
 """
 from __future__ import annotations
 
@@ -121,22 +120,46 @@ class GlobalPointCloudWarper:
         h, w = int(target_height), int(target_width)
         if points is None or points.shape[0] == 0:
             return (torch.zeros(b, 3, h, w, device=self.device), torch.zeros(b, 1, h, w, device=self.device))
-        if not use_bilinear:
-            raise NotImplementedError("render_from_camera(use_bilinear=False) is not built (reference :258-349)")
         pts, col, wts = self._dev(points), self._dev(colors), self._dev(weights).reshape(-1)
         out = torch.empty((b, 3, h, w), dtype=torch.float32, device=self.device)
         msk = torch.empty((b, 1, h, w), dtype=torch.float32, device=self.device)
         ws = self._workspace(256 + h * w * 16)
+        if not use_bilinear:
+            offs, fall = self._disc(point_size)
         for i in range(b):
             keep, cam = self._camera(transformation[i], intrinsic[i])
             with torch.cuda.device(self.device):
-                rc = self._w._lib.tcw_pc_render_bilinear(self._w._context(), _ptr(pts), _ptr(col), _ptr(wts), cam, pts.shape[0], h, w,
-                                                         float(depth_threshold), _ptr(out[i]), _ptr(msk[i]), _ptr(ws), ws.numel(),
-                                                         self._w._stream())
-            _lib.check(rc, "tcw_pc_render_bilinear")
+                if use_bilinear:
+                    rc = self._w._lib.tcw_pc_render_bilinear(self._w._context(), _ptr(pts), _ptr(col), _ptr(wts), cam, pts.shape[0],
+                                                             h, w, float(depth_threshold), _ptr(out[i]), _ptr(msk[i]), _ptr(ws),
+                                                             ws.numel(), self._w._stream())
+                else:
+                    rc = self._w._lib.tcw_pc_render_disc(self._w._context(), _ptr(pts), _ptr(col), _ptr(wts), cam, pts.shape[0], h, w,
+                                                         float(depth_threshold),
+                                                         offs.numpy().ctypes.data_as(ctypes.POINTER(ctypes.c_int)),
+                                                         fall.numpy().ctypes.data_as(ctypes.POINTER(ctypes.c_float)), fall.numel(),
+                                                         _ptr(out[i]), _ptr(msk[i]), _ptr(ws), ws.numel(), self._w._stream())
+            _lib.check(rc, "tcw_pc_render_bilinear" if use_bilinear else "tcw_pc_render_disc")
         return out, msk
 
-    def _zbuffer(self, points_3d, colors_3d, transformation_target, intrinsic_target, image_size, point_size, return_depth):
+    @staticmethod
+    def _disc(point_size: float):
+        """The stamp of ``_splat_points_to_image_with_size`` (reference :281-296): integer offsets (dx, dy) within
+        point_size / 2 of the centre, rows first, and their Gaussian falloff exp(-d^2 / (2 (point_size / 4)^2)) -- the exponent
+        in Python doubles, the exp in float32, as the reference evaluates them."""
+        radius = int(point_size / 2)
+        offs, fall = [], []
+        for dy in range(-radius, radius + 1):
+            for dx in range(-radius, radius + 1):
+                dist = (dx ** 2 + dy ** 2) ** 0.5
+                if dist <= point_size / 2:
+                    offs.append((dx, dy))
+                    fall.append(-dist ** 2 / (2 * (point_size / 4) ** 2))
+        return (torch.tensor(offs, dtype=torch.int32).reshape(-1, 2).contiguous(),
+                torch.exp(torch.tensor(fall, dtype=torch.float32)).contiguous())
+
+    def _zbuffer(self, points_3d, colors_3d, transformation_target, intrinsic_target, image_size, point_size, return_depth,
+                 first_wins: bool = False):
         h, w = int(image_size[0]), int(image_size[1])
         pts, col = self._dev(points_3d), self._dev(colors_3d)
         frame = torch.empty((1, 3, h, w), dtype=torch.float32, device=self.device)
@@ -145,8 +168,9 @@ class GlobalPointCloudWarper:
         ws = self._workspace(h * w * 8)
         keep, cam = self._camera(transformation_target[0], intrinsic_target[0])
         with torch.cuda.device(self.device):
-            rc = self._w._lib.tcw_pc_render_zbuffer(self._w._context(), _ptr(pts), _ptr(col), cam, pts.shape[0], h, w, int(point_size),
-                                                    _ptr(frame), _ptr(mask), _ptr(depth), _ptr(ws), ws.numel(), self._w._stream())
+            entry = self._w._lib.tcw_pc_render_zbuffer_first if first_wins else self._w._lib.tcw_pc_render_zbuffer
+            rc = entry(self._w._context(), _ptr(pts), _ptr(col), cam, pts.shape[0], h, w, int(point_size),
+                       _ptr(frame), _ptr(mask), _ptr(depth), _ptr(ws), ws.numel(), self._w._stream())
         _lib.check(rc, "tcw_pc_render_zbuffer")
         return (frame, mask, depth) if return_depth else (frame, mask)
 
@@ -161,3 +185,9 @@ class GlobalPointCloudWarper:
                                                         return_depth: bool = False):
         assert int(point_size) >= 1
         return self._zbuffer(points_3d, colors_3d, transformation_target, intrinsic_target, image_size, int(point_size), return_depth)
+
+    # ---- reference :650-765: the sequential loop with a strict `<` (the first of equal depths stays); point_size <= 1 clamps
+    def render_pointcloud_zbuffer_vectorized_fixed(self, points_3d, colors_3d, transformation_target, intrinsic_target,
+                                                   image_size: tuple = (576, 1024), point_size: int = 1):
+        return self._zbuffer(points_3d, colors_3d, transformation_target, intrinsic_target, image_size, int(point_size), False,
+                             first_wins=True)

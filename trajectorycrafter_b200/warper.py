@@ -265,25 +265,28 @@ class Warper:
             return self.forward_warp_batch(frame1, depth1, transformation1, transformation2, intrinsic1,
                                            intrinsic2, mask1=mask1, per_frame_max=False, mask=mask)
 
-        # twice=True (models/utils.py:296-347): forward splat, then splat back along the warped flow
+        # twice=True (models/utils.py:296-347): forward splat, then splat back along the warped flow.  The matrices are
+        # prepared once, the two range checks (:580-581) share one status word that the host reads once, at the end.
         frame1_d, depth1_d = self._dev(frame1), self._dev(depth1)
         mask1_d = self._dev(mask1) if mask1 is not None else torch.ones((b, 1, h, w), device=self.device)
-        warped_frame2, mask2, warped_depth2, flow12 = self.forward_warp_batch(
-            frame1_d, depth1_d, transformation1, transformation2, intrinsic1, intrinsic2,
-            mask1=mask1, per_frame_max=False, mask=False)
-        trans_depth1 = self.compute_transformed_points(
-            depth1_d, transformation1, transformation2, intrinsic1, intrinsic2)[:, :, :, 2, 0].contiguous()
+        M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
+        status = torch.zeros(1, dtype=torch.int32, device=self.device)
+        warped_frame2, mask2, warped_depth2, flow12 = self.forward_warp_matrices(
+            frame1_d, depth1_d, M, mask1=mask1, per_frame_max=False, mask=False, check_range=status)
+        trans_depth1 = self._project(depth1_d, M)[..., 2].contiguous()
         if mask:
             warped_frame2, mask2 = self.clean_points(warped_frame2, mask2)
             warped_depth2, _ = self.clean_points(warped_depth2, mask2)
         warped_flow, _ = self.bilinear_splatting(flow12, mask1_d, trans_depth1, flow12, None, is_image=False)
+        back_flow = -warped_flow
         twice_warped_frame1, twice_warped_mask1 = self.bilinear_splatting(
-            warped_frame2, mask2, warped_depth2.squeeze(1), -warped_flow, None, is_image=True)
+            warped_frame2, mask2, warped_depth2.squeeze(1), back_flow, None, is_image=True, _status=status)
         twice_warped_depth1, _ = self.bilinear_splatting(
-            warped_depth2, mask2, warped_depth2.squeeze(1), -warped_flow, None, is_image=False)
+            warped_depth2, mask2, warped_depth2.squeeze(1), back_flow, None, is_image=False)
         if mask:
             twice_warped_frame1, twice_warped_mask1 = self.clean_points(twice_warped_frame1, twice_warped_mask1)
             twice_warped_depth1, _ = self.clean_points(twice_warped_depth1, twice_warped_mask1)
+        self.check_status(int(status.item()))
         return twice_warped_frame1, twice_warped_mask1, twice_warped_depth1, None
 
     def compute_transformed_points(
@@ -298,15 +301,19 @@ class Warper:
         (all three components 1000 where the transformed point is behind the camera)."""
         if self.resolution is not None:
             assert depth1.shape[2:4] == self.resolution
-        b, _, h, w = depth1.shape
-        M_d = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2).to(self.device)
-        depth_d = self._dev(depth1)
+        M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
+        return self._project(self._dev(depth1), M).unsqueeze(-1)
+
+    def _project(self, depth_d: torch.Tensor, M: torch.Tensor) -> torch.Tensor:
+        """(b,1,h,w) device depth + prepared (b,30) matrices -> (b,h,w,3) projected points."""
+        b, _, h, w = depth_d.shape
+        M_d = M.to(self.device, torch.float32, non_blocking=True).contiguous()
         out = torch.empty((b, h, w, 3), dtype=torch.float32, device=self.device)
         with torch.cuda.device(self.device):
             rc = self._lib.tcw_project(self._context(), _ptr(depth_d), None, _ptr(M_d), b, b, h, w,
                                        _ptr(out), self._stream())
         _lib.check(rc, "tcw_project")
-        return out.unsqueeze(-1)
+        return out
 
     def bilinear_splatting(
         self,
@@ -316,10 +323,12 @@ class Warper:
         flow12: torch.Tensor,
         flow12_mask: Optional[torch.Tensor],
         is_image: bool = False,
+        _status: Optional[torch.Tensor] = None,
     ) -> Tuple[torch.Tensor, torch.Tensor]:
         """Drop-in for models/utils.py:422-583.  frame1 (b,c,h,w), c in 1..4; mask1 (b,1,h,w)|None;
         depth1 (b,h,w) (as the reference actually passes it; (b,1,h,w) is accepted too);
-        flow12 (b,2,h,w); flow12_mask (b,1,h,w)|None.  Returns (warped (b,c,h,w), mask (b,1,h,w))."""
+        flow12 (b,2,h,w); flow12_mask (b,1,h,w)|None.  Returns (warped (b,c,h,w), mask (b,1,h,w)).
+        ``_status`` (not in the reference): an int32 CUDA tensor the range flag is ORed into instead of being read back here."""
         if self.resolution is not None:
             assert frame1.shape[2:4] == self.resolution
         b, c, h, w = frame1.shape
@@ -332,17 +341,14 @@ class Warper:
         flags = _lib.TCW_IS_IMAGE if is_image else 0
         out = torch.empty((b, c, h, w), dtype=torch.float32, device=self.device)
         out_mask = torch.empty((b, 1, h, w), dtype=torch.float32, device=self.device)
-        flag = torch.zeros(1, dtype=torch.int32, device=self.device)
-        need = ctypes.c_size_t(0)
-        _lib.check(self._lib.tcw_workspace_bytes(self._context(), b, h, w, flags, ctypes.byref(need)),
-                   "tcw_workspace_bytes")
+        flag = _status if _status is not None else torch.zeros(1, dtype=torch.int32, device=self.device)
         ws = self._get_workspace(b, h, w, flags)
         with torch.cuda.device(self.device):
             rc = self._lib.tcw_splat(self._context(), _ptr(frame_d), _ptr(mask1_d), _ptr(depth_d), _ptr(flow_d),
                                      _ptr(fmask_d), b, c, h, w, flags, _ptr(out), _ptr(out_mask), _ptr(flag),
                                      _ptr(ws), ws.numel(), self._stream())
         _lib.check(rc, "tcw_splat")
-        if is_image:
+        if is_image and _status is None:
             self.check_status(int(flag.item()))       # models/utils.py:580-581
         if odt == torch.float64:               # float64 inputs (after clean_points) stay float64 in the reference
             out, out_mask = out.double(), out_mask.double()
