@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(WIN_PRE_WARPS * 32)
 k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
     constexpr unsigned FULL = 0xffffffffu;
     __shared__ int gb[4];
-    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, wv = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);      // the shuffle tells the compiler the warp index is uniform
     const int uc = blockIdx.y, u = unit0 + uc, ps = prep0 + uc;
     const int h = A.h, w = A.w;
     const size_t hw = (size_t)h * w;
@@ -372,16 +372,13 @@ __device__ __forceinline__ void win_step2(const WinOut& o, int lane, bool onT, i
     const float sa = o.sw[pT], sc = o.sw[pB];
     const u64 t2 = pk1(wT), b2 = pk1(wB);
     float r, g, b, z;
-    if (cT == cB) {      // both switched off: the scratch cell takes one (meaningless) write
-        o.s4[pT] = a;
-    } else {
-        upk(fma2(rg, t2, pk(a.x, a.y)), r, g); upk(fma2(bz, t2, pk(a.z, a.w)), b, z);
-        o.s4[pT] = make_float4(r, g, b, z);
-        o.sw[pT] = sa + wT;
-        upk(fma2(rg, b2, pk(c.x, c.y)), r, g); upk(fma2(bz, b2, pk(c.z, c.w)), b, z);
-        o.s4[pB] = make_float4(r, g, b, z);
-        o.sw[pB] = sc + wB;
-    }
+    // (both switched off: cT == cB == the lane's scratch cell, which takes two meaningless writes -- no branch)
+    upk(fma2(rg, t2, pk(a.x, a.y)), r, g); upk(fma2(bz, t2, pk(a.z, a.w)), b, z);
+    o.s4[pT] = make_float4(r, g, b, z);
+    o.sw[pT] = sa + wT;
+    upk(fma2(rg, b2, pk(c.x, c.y)), r, g); upk(fma2(bz, b2, pk(c.z, c.w)), b, z);
+    o.s4[pB] = make_float4(r, g, b, z);
+    o.sw[pB] = sc + wB;
     __syncwarp();
 }
 // live lanes form one run of consecutive lanes?
@@ -651,7 +648,7 @@ __global__ void __launch_bounds__(WIN_WARPS * 32, TCW_WIN_MINB)
 k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     constexpr unsigned FULL = 0xffffffffu;
     extern __shared__ __align__(16) unsigned char win_smem[];
-    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, wv = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);      // the shuffle tells the compiler the warp index is uniform
     const int strip = blockIdx.x * WIN_WARPS + wv;
     if (strip >= A.ns) return;                                           // whole warps leave together
     const int uc = blockIdx.y, u = unit0 + uc, ps = prep0 + uc, sl = slot0 + uc;
@@ -683,9 +680,19 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
         S.fm = A.gflow_mask ? A.gflow_mask + (size_t)u * hw : nullptr;
     }
     const UnitStats* st = A.stats + (A.stat_index_global >= 0 ? A.stat_index_global : u);
-    const float L = __uint_as_float(st->lbits);
+    // (values every lane loads from one address go through a shuffle from lane 0: the compiler then knows they are uniform and
+    // drops the convergence checks around the collectives of the row loop)
+    const float L = __uint_as_float(__shfl_sync(FULL, st->lbits, 0));
 
-    const WinBox b0 = A.box[(size_t)ps * A.nh + hs0], b1 = A.box[(size_t)ps * A.nh + hs0 + 1];
+    WinBox b0, b1;
+    {
+        const int4* __restrict__ bp = (const int4*)(A.box + (size_t)ps * A.nh + hs0);
+        int4 q0 = bp[0], q1 = bp[1];
+        q0.x = __shfl_sync(FULL, q0.x, 0); q0.y = __shfl_sync(FULL, q0.y, 0); q0.z = __shfl_sync(FULL, q0.z, 0);
+        q1.x = __shfl_sync(FULL, q1.x, 0); q1.y = __shfl_sync(FULL, q1.y, 0); q1.z = __shfl_sync(FULL, q1.z, 0);
+        b0.x0 = (short)(q0.x & 0xffff); b0.y0 = (short)(q0.x >> 16); b0.bw = (short)(q0.y & 0xffff); b0.bh = (short)(q0.y >> 16); b0.flags = q0.z; b0.pad = 0;
+        b1.x0 = (short)(q1.x & 0xffff); b1.y0 = (short)(q1.x >> 16); b1.bw = (short)(q1.y & 0xffff); b1.bh = (short)(q1.y >> 16); b1.flags = q1.z; b1.pad = 0;
+    }
     const int a0 = (int)b0.bw * b0.bh, a1 = (int)b1.bw * b1.bh;
     float* pilep = A.pile + ((size_t)sl * A.ns + strip) * 8;
     u64 hrg = 0, hbz = 0;
@@ -746,6 +753,7 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
                 (void)TCW_INRANGE(A.status, off >= 0 && off + cells <= A.pool_cells && cells + WIN_SCRATCH <= WIN_CAP + WIN_SCRATCH + (mode == WM_GLOBAL ? (1 << 30) : 0));
             }
             const int pitch_l = shared_plane ? w : pitch;
+            mode = __shfl_sync(FULL, mode, 0);      // uniform, and the compiler can see it (no convergence checks in the row loop)
             if (mode == WM_SMEM) {
                 o.scratch = cells;
                 {
@@ -836,7 +844,7 @@ __global__ void __launch_bounds__(128)
 k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, int tiles_x) {
     constexpr unsigned FULL = 0xffffffffu;
     __shared__ int4 cand_all[4][WIN_MAXC];                          // per warp: {x0, y0, bw | bh << 16, slab offset}
-    const int lane = threadIdx.x & 31, wv = threadIdx.x >> 5;
+    const int lane = threadIdx.x & 31, wv = __shfl_sync(0xffffffffu, threadIdx.x >> 5, 0);      // the shuffle tells the compiler the warp index is uniform
     int4* cand = cand_all[wv];
     __shared__ int hitl_all[4][32];
     int* hitl = hitl_all[wv];
