@@ -494,7 +494,8 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
             N.out_frame = J.out; N.out_mask = (float*)J.out_mask;
         }
         prof_begin(ctx, PK_NORMALISE, nu, sk);
-        k_gather_normalise<<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
+        if (N.out_c == 3 && N.is_image && N.out_depth) k_gather_normalise<true><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
+        else k_gather_normalise<false><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
         prof_end(ctx, sk);
         LAUNCH_CHECK("k_gather_normalise");
         if (clean) {

@@ -840,6 +840,9 @@ struct WinNormArgs {
     int mask_u8;                          // out_mask is a uint8 buffer (TCW_MASK_U8)
 };
 
+// IMG3: the forward warp's own shape -- three colour planes (holes -1, range check, clamp) and a depth plane -- with the
+// branches of the generic store loop resolved at compile time and 32-bit byte offsets from one uniform base per output.
+template <bool IMG3>
 __global__ void __launch_bounds__(128)
 k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, int tiles_x) {
     constexpr unsigned FULL = 0xffffffffu;
@@ -966,7 +969,34 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
     }
     // ---- normalise, mask, clip (models/utils.py:571-583)
     bool bad = false;
-    if (tx < w && row0 < h) {
+    if (IMG3) {
+        if (tx < w && row0 < h) {
+            // byte offsets fit 32 bits: 3 * h * w * 4 < 2^32 (h * w < 2^28 is checked at submission)
+            char* __restrict__ fb = (char*)(N.out_frame + (size_t)u * 3 * hw);
+            char* __restrict__ db = (char*)(N.out_depth + (size_t)u * hw);
+            char* __restrict__ mb = (char*)N.out_mask + (size_t)u * hw * (N.mask_u8 ? 1 : 4);
+            const unsigned hw4 = (unsigned)hw * 4u, w4 = (unsigned)w * 4u;
+            unsigned off = ((unsigned)row0 * (unsigned)w + (unsigned)tx) * 4u;
+            const int nr = R1 - row0;
+            #pragma unroll
+            for (int r = 0; r < 8; ++r) {
+                if (r >= nr) break;
+                const float W = accw[r];
+                const bool valid = W > 0.0f;
+                float rr = rcp_approx(W);
+                rr = fmaf(rr, fmaf(-W, rr, 1.0f), rr);
+                const float x0 = valid ? acc[r].x * rr : -1.0f, x1 = valid ? acc[r].y * rr : -1.0f, x2 = valid ? acc[r].z * rr : -1.0f;
+                bad |= !(fabsf(x0) <= 1.1f) | !(fabsf(x1) <= 1.1f) | !(fabsf(x2) <= 1.1f);      // (a NaN fails too, as in the reference's assert)
+                __stcs((float*)(fb + off), clampf(x0, -1.0f, 1.0f));
+                __stcs((float*)(fb + (off + hw4)), clampf(x1, -1.0f, 1.0f));
+                __stcs((float*)(fb + (off + 2u * hw4)), clampf(x2, -1.0f, 1.0f));
+                __stcs((float*)(db + off), valid ? acc[r].w * rr : 0.0f);
+                if (N.mask_u8) *(unsigned char*)(mb + (off >> 2)) = valid ? 1 : 0;
+                else __stcs((float*)(mb + off), valid ? 1.0f : 0.0f);
+                off += w4;
+            }
+        }
+    } else if (tx < w && row0 < h) {
         const size_t p0 = (size_t)row0 * w + tx;
         float* o0 = N.out_frame + (size_t)u * N.out_c * hw + p0;
         float* om = N.out_mask + (size_t)u * hw + p0;
