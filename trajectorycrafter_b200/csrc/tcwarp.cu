@@ -421,7 +421,8 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
     win_layout(ctx, n_units, h, w, J.flags, &L);
     if (!workspace || workspace_bytes < L.total) return fail(TCW_E_WORKSPACE, "tcw: workspace too small (see tcw_workspace_bytes)");
     if (!ctx->win_smem_set) {
-        CUDA_TRY(cudaFuncSetAttribute(k_splat_window, cudaFuncAttributeMaxDynamicSharedMemorySize, WIN_WARPS * WIN_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(k_splat_window<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIN_WARPS * WIN_BYTES));
+        CUDA_TRY(cudaFuncSetAttribute(k_splat_window<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, WIN_WARPS * WIN_BYTES));
         ctx->win_smem_set = 1;
     }
     char* ws = (char*)workspace;
@@ -480,7 +481,8 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
             CUDA_TRY(cudaMemsetAsync(A.spill_flag + slot0, 0, (size_t)nu * sizeof(int), sk));
         }
         prof_begin(ctx, PK_SPLAT, nu, sk);
-        k_splat_window<<<dim3(g2d.x, nu), WIN_WARPS * 32, WIN_WARPS * WIN_BYTES, sk>>>(A, u0, prep0, slot0);
+        if (A.fused) k_splat_window<true><<<dim3(g2d.x, nu), WIN_WARPS * 32, WIN_WARPS * WIN_BYTES, sk>>>(A, u0, prep0, slot0);
+        else k_splat_window<false><<<dim3(g2d.x, nu), WIN_WARPS * 32, WIN_WARPS * WIN_BYTES, sk>>>(A, u0, prep0, slot0);
         prof_end(ctx, sk);
         LAUNCH_CHECK("k_splat_window");
         WinNormArgs N;

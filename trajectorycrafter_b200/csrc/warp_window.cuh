@@ -398,7 +398,7 @@ struct WinSrc {
 
 // The eight rows of a strip in one mode.  `act` = this lane's half takes part in this pass; pitch / idbase = this lane's
 // window (padded floor coordinates -> cell index of the pass allocation: id = iy * pitch + ix + idbase).
-template <int MODE>
+template <int MODE, bool FUSED>
 __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc& S, const WinOut& o, int lane, int x0s, int y0, int y1,
                                                   bool act, int pitch, int idbase, float L, u64& hrg, u64& hbz, float& hwt, bool& any_pile) {
     constexpr unsigned FULL = 0xffffffffu;
@@ -421,9 +421,22 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
     const u64 rL2 = pk1(rL), nL2 = pk1(-L);
 
     float flxA_n, flxB_n, flyA_n, flyB_n, zA_n, zB_n, vA_n[4], vB_n[4], mA_n = 1.f, mB_n = 1.f;
+    const unsigned hw4 = hw32 * 4u;
     auto load_row = [&](int y) {
         const unsigned q = (unsigned)y * (unsigned)w;
-        if (vec2all) {
+        if (FUSED && vec2all) {
+            // the forward warp's own sources: flow x / y planes, z', three colour planes h*w apart, an optional mask; no fourth
+            // value, no flow mask.  Byte offsets fit 32 bits (3 * h * w * 4 < 2^32: h * w < 2^28 is checked at submission)
+            const unsigned qb = (q + colA) * 4u;
+            const float2 f0 = __ldcg((const float2*)((const char*)S.fl + qb)), f1 = __ldcg((const float2*)((const char*)S.fl + (qb + hw4)));
+            const float2 z2 = __ldcg((const float2*)((const char*)S.wd + qb));
+            const float2 t0 = __ldg((const float2*)((const char*)S.v[0] + qb)), t1 = __ldg((const float2*)((const char*)S.v[0] + (qb + hw4)));
+            const float2 t2 = __ldg((const float2*)((const char*)S.v[0] + (qb + 2u * hw4)));
+            flxA_n = f0.x; flxB_n = f0.y; flyA_n = f1.x; flyB_n = f1.y; zA_n = z2.x; zB_n = z2.y;
+            vA_n[0] = t0.x; vB_n[0] = t0.y; vA_n[1] = t1.x; vB_n[1] = t1.y; vA_n[2] = t2.x; vB_n[2] = t2.y; vA_n[3] = 0.f; vB_n[3] = 0.f;
+            mA_n = 1.f; mB_n = 1.f;
+            if (S.m1) { const float2 t = __ldg((const float2*)((const char*)S.m1 + qb)); mA_n = t.x; mB_n = t.y; }
+        } else if (vec2all) {
             const unsigned qa = q + colA;
             const float2 f0 = __ldcg((const float2*)(S.fl + qa)), f1 = __ldcg((const float2*)(S.fl + hw32 + qa));
             const float2 z2 = __ldcg((const float2*)(S.wd + qa));
@@ -488,12 +501,12 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
             if (Lok) qd = div2_with_rcp(ld, nL2, rL2);
             else qd = pk(__fdiv_rn(plo(ld), L), __fdiv_rn(phi(ld), L));
             mg2 = exp2x(mul2(qd, pk1(-50.0f)));
-            if (S.m1 || S.fm) mg2 = mul2(mg2, pk(mA, mB));
+            if (S.m1 || (!FUSED && S.fm)) mg2 = mul2(mg2, pk(mA, mB));
         }
         float mgA, mgB;
         upk(mg2, mgA, mgB);
         // values of the two pixels: (v0, v1), (v2, v3); the fused path splats z' itself as the fourth value
-        const float z3A = A.fused ? zA : vA[3], z3B = A.fused ? zB : vB[3];
+        const float z3A = FUSED ? zA : vA[3], z3B = FUSED ? zB : vB[3];
         u64 rgA = pk(vA[0], vA[1]), bzA = pk(vA[2], z3A), rgB = pk(vB[0], vB[1]), bzB = pk(vB[2], z3B);
         if (pileA || pileB) {      // exactly on padded cell (2,2): four unit-proximity hits on output pixel (1,1) (behind-camera points)
             any_pile = true;
@@ -644,6 +657,7 @@ __device__ __forceinline__ void splat_window_rows(const WinArgs& A, const WinSrc
 #ifndef TCW_WIN_MINB
 #define TCW_WIN_MINB (12 / TCW_WIN_WARPS)
 #endif
+template <bool FUSED>      // FUSED: the forward warp (sources = K1's flow / z' + the frame); else the generic splat of tcw_splat
 __global__ void __launch_bounds__(WIN_WARPS * 32, TCW_WIN_MINB)
 k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     constexpr unsigned FULL = 0xffffffffu;
@@ -665,7 +679,7 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
 
     // sources of this unit
     WinSrc S;
-    if (A.fused) {
+    if (FUSED) {
         const int s = win_src(A, u);
         S.fl = A.flow_out ? A.flow_out + (size_t)u * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
         S.wd = A.zbuf + (size_t)ps * hw;
@@ -763,7 +777,7 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
                     for (int i = lane; i < nw; i += 32) o.sw[i] = 0.f;
                     __syncwarp();
                 }
-                splat_window_rows<WM_SMEM>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
+                splat_window_rows<WM_SMEM, FUSED>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
                 __syncwarp();
                 // the window becomes a dense slab (cells in window order == slab order)
                 // (four cells per lane and trip: the shared-memory reads of a trip are issued before its global stores)
@@ -790,7 +804,7 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
                     __threadfence();      // the zeros are in L2 before this warp's first reduction arrives
                     __syncwarp();
                 }
-                splat_window_rows<WM_GLOBAL>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
+                splat_window_rows<WM_GLOBAL, FUSED>(A, S, o, lane, sx * 64, y0, y1, act, pitch_l, idbase, L, hrg, hbz, hwt, any_pile);
             }
             if (!shared_plane) {
                 if (uni) off0 = (int)off;
