@@ -139,22 +139,27 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
         const bool vec2 = __all_sync(FULL, okB || !okA) && !(w & 1) &&
             !((((size_t)dp) | ((size_t)flp) | ((size_t)zp) | ((size_t)gfl)) & 7);
         // the strip's depth values up front: eight independent loads in flight instead of one per row
+        // (32-bit byte offsets from the unit's plane bases: 2 * h * w * 4 < 2^32, h * w < 2^28 is checked at submission)
+        const unsigned w4 = (unsigned)w * 4u, hw4 = (unsigned)hw * 4u;
+        const unsigned oA0 = ((unsigned)y0 * (unsigned)w + (unsigned)cA) * 4u, oB0 = ((unsigned)y0 * (unsigned)w + (unsigned)cB) * 4u;
+        const int nr = y1 - y0;
         float2 dpre[8];
         if (PROJECT) {
             #pragma unroll
             for (int r = 0; r < 8; ++r) {
-                const int y = y0 + r < y1 ? y0 + r : y1 - 1;
-                const size_t qA = (size_t)y * w + cA, qB = (size_t)y * w + cB;
-                if (vec2) dpre[r] = __ldg((const float2*)(dp + qA));
-                else dpre[r] = make_float2(__ldg(dp + qA), __ldg(dp + qB));
+                dpre[r] = make_float2(0.f, 0.f);
+                if (r < nr) {
+                    if (vec2) dpre[r] = __ldg((const float2*)((const char*)dp + (oA0 + r * w4)));
+                    else dpre[r] = make_float2(__ldg((const float*)((const char*)dp + (oA0 + r * w4))), __ldg((const float*)((const char*)dp + (oB0 + r * w4))));
+                }
             }
         }
         #pragma unroll
         for (int r = 0; r < 8; ++r) {
             const int y = y0 + r;
-            if (y >= y1) break;
+            if (r >= nr) break;
             const float fy = (float)y;
-            const size_t qA = (size_t)y * w + cA, qB = (size_t)y * w + cB;
+            const unsigned oA = oA0 + r * w4, oB = oB0 + r * w4;
             float flxA, flxB, flyA, flyB, zA, zB;
             if (PROJECT) {
                 const float dA = dpre[r].x, dB = dpre[r].y;
@@ -215,22 +220,26 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
                 upk(flx2, flxA, flxB);
                 upk(fly2, flyA, flyB);
                 zA = P2A; zB = P2B;
+                char* __restrict__ fb = (char*)flp;
+                char* __restrict__ zb = (char*)zp;
                 if (vec2) {
                     if (okA) {
-                        __stcg((float2*)(flp + qA), make_float2(flxA, flxB)); __stcg((float2*)(flp + hw + qA), make_float2(flyA, flyB));
-                        __stcg((float2*)(zp + qA), make_float2(zA, zB));
+                        __stcg((float2*)(fb + oA), make_float2(flxA, flxB)); __stcg((float2*)(fb + (oA + hw4)), make_float2(flyA, flyB));
+                        __stcg((float2*)(zb + oA), make_float2(zA, zB));
                     }
                 } else {
-                    if (okA) { __stcg(flp + qA, flxA); __stcg(flp + hw + qA, flyA); __stcg(zp + qA, zA); }
-                    if (okB) { __stcg(flp + qB, flxB); __stcg(flp + hw + qB, flyB); __stcg(zp + qB, zB); }
+                    if (okA) { __stcg((float*)(fb + oA), flxA); __stcg((float*)(fb + (oA + hw4)), flyA); __stcg((float*)(zb + oA), zA); }
+                    if (okB) { __stcg((float*)(fb + oB), flxB); __stcg((float*)(fb + (oB + hw4)), flyB); __stcg((float*)(zb + oB), zB); }
                 }
             } else {
+                const char* __restrict__ gb = (const char*)gfl;
+                const char* __restrict__ db = (const char*)dp;
                 if (vec2) {
-                    const float2 f0 = __ldg((const float2*)(gfl + qA)), f1 = __ldg((const float2*)(gfl + hw + qA)), z2 = __ldg((const float2*)(dp + qA));
+                    const float2 f0 = __ldg((const float2*)(gb + oA)), f1 = __ldg((const float2*)(gb + (oA + hw4))), z2 = __ldg((const float2*)(db + oA));
                     flxA = f0.x; flxB = f0.y; flyA = f1.x; flyB = f1.y; zA = z2.x; zB = z2.y;
                 } else {
-                    flxA = __ldg(gfl + qA); flyA = __ldg(gfl + hw + qA); zA = __ldg(dp + qA);
-                    flxB = __ldg(gfl + qB); flyB = __ldg(gfl + hw + qB); zB = __ldg(dp + qB);
+                    flxA = __ldg((const float*)(gb + oA)); flyA = __ldg((const float*)(gb + (oA + hw4))); zA = __ldg((const float*)(db + oA));
+                    flxB = __ldg((const float*)(gb + oB)); flyB = __ldg((const float*)(gb + (oB + hw4))); zB = __ldg((const float*)(db + oB));
                 }
             }
             // same arithmetic as K2 (models/utils.py:450-452): off = (flow + grid) + 1
