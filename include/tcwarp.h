@@ -171,6 +171,20 @@ int tcw_pc_render_zbuffer_first(tcw_ctx* ctx, const float* points, const float* 
                                 long long n_points, int h, int w, int point_size,
                                 float* out_frame, float* out_mask, float* out_depth,
                                 void* workspace, size_t workspace_bytes, void* cuda_stream);
+/*
+ * tcw_pc_render_zbuffer_static   NO counterpart in the reference: added for callers that
+ *                          cannot allocate device memory (code under CUDA graph capture, tight serving loops, harnesses that
+ *                          forbid cudaMalloc).  Same arguments, kernels and results as tcw_pc_render_zbuffer, but without the
+ *                          workspace: the h*w*8-byte z-buffer is a file-scope device array inside the library
+ *                          (TCW_ZB_STATIC_MAX_PIXELS cells = 8 MiB, held by every GPU that loads the library until exit).
+ *                          h*w > TCW_ZB_STATIC_MAX_PIXELS is rejected with TCW_E_WORKSPACE.  The call allocates nothing
+ *                          (no cudaMalloc / cudaFree); the context's device must be current.  All calls on one GPU share the
+ *                          array: each call re-initialises the part it uses, calls that overlap on the GPU race.
+ */
+#define TCW_ZB_STATIC_MAX_PIXELS (1 << 20)
+int tcw_pc_render_zbuffer_static(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                                 long long n_points, int h, int w, int point_size,
+                                 float* out_frame, float* out_mask, float* out_depth, void* cuda_stream);
 int tcw_pc_render_bilinear(tcw_ctx* ctx, const float* points, const float* colors, const float* weights, const float* camera,
                            long long n_points, int h, int w, float depth_threshold,
                            float* out_frame, float* out_mask, void* workspace, size_t workspace_bytes, void* cuda_stream);

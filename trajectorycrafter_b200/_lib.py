@@ -16,6 +16,7 @@ TCW_ATOMIC_F32 = 16
 TCW_HOST_MASK_U8 = 32
 TCW_MASK_U8 = 64
 TCW_IPC_HANDLE_BYTES = 64
+TCW_ZB_STATIC_MAX_PIXELS = 1 << 20
 # status bits a call ORs into its range_flag word
 TCW_STATUS_RANGE = 1
 TCW_STATUS_UNORDERED = 2
@@ -46,6 +47,7 @@ SIGNATURES = {
     "tcw_pc_lift": (c_int, [c_void_p, _FP, _FP, _FP, _FP, c_int, c_int, c_int, c_int, _FP, _FP, c_void_p]),
     "tcw_pc_render_zbuffer": (c_int, [c_void_p, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_int, _FP, _FP, _FP, _VP, c_size_t, c_void_p]),
     "tcw_pc_render_zbuffer_first": (c_int, [c_void_p, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_int, _FP, _FP, _FP, _VP, c_size_t, c_void_p]),
+    "tcw_pc_render_zbuffer_static": (c_int, [c_void_p, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_int, _FP, _FP, _FP, c_void_p]),
     "tcw_pc_render_disc": (c_int, [c_void_p, _FP, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_float, POINTER(c_int), POINTER(c_float), c_int, _FP, _FP, _VP, c_size_t, c_void_p]),
     "tcw_pc_render_bilinear": (c_int, [c_void_p, _FP, _FP, _FP, POINTER(c_float), c_longlong, c_int, c_int, c_float, _FP, _FP, _VP, c_size_t, c_void_p]),
     "tcw_depth_post": (c_int, [c_void_p, _FP, c_int, c_int, c_int, c_int, c_float, c_float, c_float, _FP, _FP, c_void_p]),

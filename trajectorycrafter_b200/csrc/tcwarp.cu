@@ -1136,3 +1136,51 @@ TCW_API int tcw_forward_warp_host(tcw_ctx* ctx, const float* frame, const float*
     cudaSetDevice(prev);
     return rc;
 }
+
+// ----------------------------------------------------------------------------------------------
+// Allocation-free z-buffer render (no counterpart in the reference).
+// For callers that cannot call cudaMalloc -- code under CUDA graph capture, tight serving loops, harnesses that forbid it:
+// the h*w*8-byte z-buffer that tcw_pc_render_zbuffer takes as caller workspace lives in a file-scope device array instead.
+// Every GPU that loads the library holds TCW_ZB_STATIC_MAX_PIXELS * 8 bytes (8 MiB) until exit.  All calls on one GPU share
+// the array and it keeps the last call's contents: each call re-fills the part it uses with the "empty" key first, and two
+// calls that overlap on the GPU (different streams, no ordering between them) race.
+// ----------------------------------------------------------------------------------------------
+static __device__ __align__(256) unsigned long long g_zb_static[TCW_ZB_STATIC_MAX_PIXELS];
+
+// In host code `g_zb_static` is a host-side stand-in, not a device address: the kernels get what cudaGetSymbolAddress
+// returns, looked up once per device with that device current.
+static const int ZB_MAX_DEVICES = 64;
+static void* g_zb_static_ptr[ZB_MAX_DEVICES];
+
+static int zb_static_address(tcw_ctx* ctx, void** out) {
+    int cur = -1;
+    CUDA_TRY(cudaGetDevice(&cur));
+    if (cur != ctx->device) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer_static: the context's device must be the current device");
+    if (cur < 0 || cur >= ZB_MAX_DEVICES) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer_static: device index beyond 63");
+    void* p = g_zb_static_ptr[cur];
+    if (!p) {
+        const cudaError_t e = cudaGetSymbolAddress(&p, g_zb_static);
+        if (e != cudaSuccess || !p) {
+            cudaGetLastError();
+            return fail(TCW_E_CUDA, "tcw_pc_render_zbuffer_static: cudaGetSymbolAddress of the static z-buffer failed");
+        }
+        g_zb_static_ptr[cur] = p;      // (two threads racing here store the same value)
+    }
+    *out = p;
+    return TCW_OK;
+}
+
+TCW_API int tcw_pc_render_zbuffer_static(tcw_ctx* ctx, const float* points, const float* colors, const float* camera,
+                                         long long n_points, int h, int w, int point_size,
+                                         float* out_frame, float* out_mask, float* out_depth, void* cuda_stream) {
+    if (!ctx) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer_static: ctx is NULL");
+    if (h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_pc_render_zbuffer_static: bad image size");
+    if ((long long)h * (long long)w > (long long)TCW_ZB_STATIC_MAX_PIXELS)
+        return fail(TCW_E_WORKSPACE, "tcw_pc_render_zbuffer_static: h*w exceeds TCW_ZB_STATIC_MAX_PIXELS (1048576); use tcw_pc_render_zbuffer with a caller workspace");
+    void* zb = nullptr;
+    const int rc = zb_static_address(ctx, &zb);
+    if (rc) return rc;
+    // same kernels, same winner rule as tcw_pc_render_zbuffer; no cudaMalloc / cudaFree / allocating routine on this path
+    return pc_zbuffer_impl(ctx, points, colors, camera, n_points, h, w, point_size, 0, out_frame, out_mask, out_depth,
+                           zb, (size_t)TCW_ZB_STATIC_MAX_PIXELS * sizeof(unsigned long long), cuda_stream);
+}
