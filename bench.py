@@ -605,6 +605,39 @@ def run_ours(args):
                 "achieved_GBps": p_bytes / (p_ms * 1e-3) / 1e9, "frac_of_hbm_peak": p_bytes / (p_ms * 1e-3) / 1e9 / peak,
                 "note": "includes the two torch.empty output allocations of the Python entry; 462 MB in + 202 MB out, larger than L2"}
         del pf, pm
+        # the same lines fused behind the warp (tcw_forward_warp_pack) against the two calls, on the reference's own shapes:
+        # 49 frames warped at 576x1024 (demo.py:545-547), condition video at 384x672
+        from trajectorycrafter_b200.workloads import orbit_units as _orb, synthetic_clip as _clip
+        bf, bd = _clip(N_FRAMES, Hs, Ws, seed=5)
+        bT1, bT2, bK, _ = _orb(bd, Hs, Ws, presets=[(0, 30)])
+        bf, bd = bf.to(dev), bd.to(dev)
+        bflag = torch.zeros(1, dtype=torch.int32, device=dev)
+
+        def two_calls():
+            wf, wm, _, _ = warper.forward_warp_batch(bf, bd, bT1, bT2, bK, check_range=bflag)
+            return warper.pack_condition(wf, wm, (H, W))
+
+        def fused():
+            return warper.forward_warp_pack(bf, bd, bT1, bT2, bK, None, (H, W), check_range=bflag)
+        res = {}
+        for name, fn in (("warp_then_pack", two_calls), ("fused", fused)):
+            for _ in range(3):
+                r_ = fn()
+            torch.cuda.synchronize()
+            p0.record()
+            for _ in range(10):
+                r_ = fn()
+            p1.record()
+            torch.cuda.synchronize()
+            res[name] = p0.elapsed_time(p1) / 10
+        same = bool(torch.equal(two_calls()[0], fused()[0]) and torch.equal(two_calls()[1], fused()[1]))
+        px = N_FRAMES * Hs * Ws
+        pack["fused_behind_warp"] = {"warp_then_pack_ms": res["warp_then_pack"], "fused_ms": res["fused"],
+                                     "Mpix_per_s_fused": px / (res["fused"] * 1e-3) / 1e6, "bit_identical": same,
+                                     "result_bytes_per_warped_px": {"warp_then_pack": 28 + 16 * H * W / (Hs * Ws), "fused": 16 * H * W / (Hs * Ws)},
+                                     "what": f"{N_FRAMES} units warped at {Hs}x{Ws}, condition video + masks at {H}x{W}; device time incl. the "
+                                             "host-side matrix preparation and output allocation of the Python entries"}
+        del bf, bd, r_
 
     # ---- the other SURVEY 8(f) rows, reported beside the metric, never part of it
     extras = None

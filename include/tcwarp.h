@@ -40,6 +40,7 @@ extern "C" {
                                   out_frame / out_mask pointing into a peer GPU's memory (tcw_ipc_open) this is the fused form of the
                                   exchange that assembles the condition video on the denoiser's rank: 13 B per pixel over NVLink,
                                   stored by the gather kernel itself (the consumer is reference demo.py:117-148) */
+#define TCW_PACK         128   /* tcw_workspace_bytes only: size the workspace for tcw_forward_warp_pack (tcw_forward_warp rejects the flag) */
 
 /* bits of *range_flag (status word) */
 #define TCW_STATUS_RANGE       1   /* a valid colour left [-1.1, 1.1] before the clamp: the reference's assert (models/utils.py:580-581) */
@@ -137,6 +138,21 @@ int tcw_clean_points(tcw_ctx* ctx, const float* frame, const float* mask2, int c
  */
 int tcw_resize_pack(tcw_ctx* ctx, const float* frame, const float* mask, int n, int H, int W, int h, int w,
                     float* out_video, float* out_masks, void* cuda_stream);
+
+/*
+ * The warp loop AND the lines after it in one submission (reference demo.py:77-100, 117-120): what tcw_forward_warp followed
+ * by tcw_resize_pack produces, bit for bit, without the full-resolution outputs ever reaching the caller (or HBM: the colour
+ * and mask of a chunk of units stay in the workspace, L2-resident, until k_resize_pack has read them).  For callers that only
+ * keep `warped, mask, _, _` to build the condition video -- every shipped pipeline; at 576x1024 -> 384x672 the results shrink
+ * from 28 to 7 bytes per warped pixel, which is also what a multi-GPU exchange then has to carry.
+ *   inputs as tcw_forward_warp at warp resolution H x W; flags: 0 or TCW_PER_UNIT_MAX;
+ *   out_video (3, n_units, h, w), out_masks (1, n_units, h, w) float32 DEVICE; range_flag as tcw_forward_warp;
+ *   workspace >= tcw_workspace_bytes(ctx, n_units, H, W, flags | TCW_PACK, ...).
+ */
+int tcw_forward_warp_pack(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                          const int* src_index, const float* M, int n_units, int n_src, int H, int W, int h, int w,
+                          int flags, float* out_video, float* out_masks, int* range_flag,
+                          void* workspace, size_t workspace_bytes, void* cuda_stream);
 
 /*
  * The fork's global point-cloud renderer (reference notebooks/06_10_25_vggt/warper_point_cloud.py, GlobalPointCloudWarper).

@@ -15,6 +15,7 @@ TCW_IS_IMAGE = 8
 TCW_ATOMIC_F32 = 16
 TCW_HOST_MASK_U8 = 32
 TCW_MASK_U8 = 64
+TCW_PACK = 128
 TCW_IPC_HANDLE_BYTES = 64
 TCW_ZB_STATIC_MAX_PIXELS = 1 << 20
 # status bits a call ORs into its range_flag word
@@ -39,6 +40,8 @@ SIGNATURES = {
                                  _VP, _VP, _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
     "tcw_forward_warp_host": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int,
                                       _VP, _VP, _FP, _FP, POINTER(c_int)]),
+    "tcw_forward_warp_pack": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int, c_int, c_int,
+                                      _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
     "tcw_project": (c_int, [c_void_p, _FP, _IP, _FP, c_int, c_int, c_int, c_int, _FP, c_void_p]),
     "tcw_splat": (c_int, [c_void_p, _FP, _FP, _FP, _FP, _FP, c_int, c_int, c_int, c_int, c_int,
                           _FP, _FP, _IP, _VP, c_size_t, c_void_p]),

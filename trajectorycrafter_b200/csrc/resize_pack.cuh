@@ -29,7 +29,9 @@ __device__ __forceinline__ int near_tap(int dst, int in, int out, float scale) {
 
 __global__ void __launch_bounds__(256)
 k_resize_pack(const float* __restrict__ frame, const float* __restrict__ mask, int n, int H, int W, int h, int w,
-              float sy, float sx, float* __restrict__ out_video, float* __restrict__ out_masks) {
+              float sy, float sx, float* __restrict__ out_video, float* __restrict__ out_masks, int n_total, int f0) {
+    // the n frames given are frames f0 .. f0+n-1 of an output clip of n_total frames (the fused epilogue of tcw_forward_warp_pack
+    // hands over one chunk of units at a time; the standalone entry passes n_total = n, f0 = 0)
     const size_t hw = (size_t)h * w, HW = (size_t)H * W;
     const size_t total = (size_t)n * hw;
     for (size_t p = (size_t)blockIdx.x * blockDim.x + threadIdx.x; p < total; p += (size_t)gridDim.x * blockDim.x) {
@@ -46,9 +48,9 @@ k_resize_pack(const float* __restrict__ frame, const float* __restrict__ mask, i
             const float cc = __fmul_rn(__fadd_rn(__ldg(s + r1 + tx.i0), 1.0f), 0.5f), d = __fmul_rn(__fadd_rn(__ldg(s + r1 + tx.i1), 1.0f), 0.5f);
             const float t0 = __fadd_rn(__fmul_rn(a, tx.l0), __fmul_rn(b, tx.l1));
             const float t1 = __fadd_rn(__fmul_rn(cc, tx.l0), __fmul_rn(d, tx.l1));
-            __stcs(out_video + ((size_t)c * n + f) * hw + q, __fadd_rn(__fmul_rn(t0, ty.l0), __fmul_rn(t1, ty.l1)));
+            __stcs(out_video + ((size_t)c * n_total + f0 + f) * hw + q, __fadd_rn(__fmul_rn(t0, ty.l0), __fmul_rn(t1, ty.l1)));
         }
         const float m = __ldg(mask + (size_t)f * HW + (size_t)near_tap(y, H, h, sy) * W + near_tap(x, W, w, sx));
-        __stcs(out_masks + p, __fmul_rn(__fsub_rn(1.0f, m), 255.0f));
+        __stcs(out_masks + (size_t)f0 * hw + p, __fmul_rn(__fsub_rn(1.0f, m), 255.0f));
     }
 }

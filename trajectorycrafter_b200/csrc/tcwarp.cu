@@ -400,7 +400,8 @@ static void win_layout(const tcw_ctx* ctx, int n_units, int h, int w, int flags,
     L->o_poolw = take((size_t)L->S * L->pool_cells * sizeof(float) + 256);
     L->o_spill4 = take((size_t)L->S * hw * sizeof(float4));
     L->o_spillw = take((size_t)L->S * hw * sizeof(float));
-    L->o_tmp = (flags & TCW_CLEAN) ? take((size_t)L->S * 4 * hw * sizeof(float)) : 0;      // fp32 colour + mask ahead of clean_points
+    // fp32 colour + mask ahead of clean_points; colour + mask + depth ahead of the fused resize + pack (TCW_PACK)
+    L->o_tmp = (flags & (TCW_CLEAN | TCW_PACK)) ? take((size_t)L->S * ((flags & TCW_PACK) ? 5 : 4) * hw * sizeof(float)) : 0;
     L->total = off;
 }
 
@@ -410,6 +411,8 @@ struct WinJob {
     float* out; int out_c;             // (n, out_c, h, w) fp32, or (with TCW_CLEAN) the float64 frame
     void* out_mask; float* out_depth;
     int is_image; int* range_flag;
+    // TCW_PACK: the chunk's colour / mask go to scratch and k_resize_pack writes (3, n, pack_h, pack_w) / (1, n, pack_h, pack_w)
+    int pack_h, pack_w; float* pack_video; float* pack_masks;
 };
 
 static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* workspace, size_t workspace_bytes, cudaStream_t st) {
@@ -426,7 +429,7 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
         ctx->win_smem_set = 1;
     }
     char* ws = (char*)workspace;
-    const bool per_unit = J.flags & TCW_PER_UNIT_MAX, clean = J.flags & TCW_CLEAN;
+    const bool per_unit = J.flags & TCW_PER_UNIT_MAX, clean = J.flags & TCW_CLEAN, pack = J.flags & TCW_PACK;
     A.strips_x = L.strips_x; A.ns = L.ns; A.nh = L.nh; A.ng = L.ng;
     A.stats = (const UnitStats*)(ws + CTRL_BYTES); A.stats_rw = (UnitStats*)(ws + CTRL_BYTES);
     A.stat_index_global = per_unit ? -1 : n_units; A.n_units_total = n_units;
@@ -437,7 +440,7 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
     A.pool4 = (float4*)(ws + L.o_pool4); A.poolw = (float*)(ws + L.o_poolw); A.pool_cells = L.pool_cells; A.n_slots = L.S;
     A.spill4 = (float4*)(ws + L.o_spill4); A.spillw = (float*)(ws + L.o_spillw);
     A.status = J.range_flag;
-    float* tmp = clean ? (float*)(ws + L.o_tmp) : nullptr;
+    float* tmp = (clean || pack) ? (float*)(ws + L.o_tmp) : nullptr;
     const int NL = L.NL, g2 = L.g2;
     int rc = ensure_lanes(ctx, NL);
     if (rc) return rc;
@@ -492,6 +495,13 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
             // fp32 results of the chunk go to scratch (laid out as units u0.. of a (n,3,h,w) / (n,1,h,w) pair), clean_points makes them float64
             N.out_frame = tmp + (size_t)slot0 * 4 * hw - (size_t)u0 * J.out_c * hw;
             N.out_mask = tmp + (size_t)slot0 * 4 * hw + (size_t)nu * J.out_c * hw - (size_t)u0 * hw;
+        } else if (pack) {
+            // the chunk's results stay in scratch (L2-resident: a slot is reused every NL chunks), laid out as units u0.. of
+            // (n,3,h,w) | (n,1,h,w) | (n,1,h,w); the depth plane only keeps the gather on its specialised store loop
+            float* base = tmp + (size_t)slot0 * 5 * hw;
+            N.out_frame = base - (size_t)u0 * 3 * hw;
+            N.out_mask = base + (size_t)nu * 3 * hw - (size_t)u0 * hw;
+            N.out_depth = base + (size_t)nu * 4 * hw - (size_t)u0 * hw;
         } else {
             N.out_frame = J.out; N.out_mask = (float*)J.out_mask;
         }
@@ -506,6 +516,15 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
             k_clean_points<<<dim3(ctx_x * cty, nu), TILE_THREADS, 0, sk>>>(tf, tf + (size_t)nu * J.out_c * hw, J.out_c, h, w, ctx_x,
                                                                           (double*)J.out + (size_t)u0 * J.out_c * hw, (double*)J.out_mask + (size_t)u0 * hw);
             LAUNCH_CHECK("k_clean_points");
+        }
+        if (pack) {      // demo.py:91-100,117-120 on the chunk's units while their colour / mask are L2-hot
+            const float* tf = tmp + (size_t)slot0 * 5 * hw;
+            const size_t total = (size_t)nu * J.pack_h * J.pack_w, want = (total + 255) / 256;
+            const int blocks = (int)(want < (size_t)ctx->sm_count * 8 ? want : (size_t)ctx->sm_count * 8);
+            k_resize_pack<<<blocks, 256, 0, sk>>>(tf, tf + (size_t)nu * 3 * hw, nu, h, w, J.pack_h, J.pack_w,
+                                                  (float)h / (float)J.pack_h, (float)w / (float)J.pack_w,
+                                                  J.pack_video, J.pack_masks, n_units, u0);
+            LAUNCH_CHECK("k_resize_pack");
         }
     }
     for (int i = 0; i + 1 < NL; ++i) {
@@ -620,6 +639,7 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
     if (n_units <= 0 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp: bad shape");
     if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp: src_index is NULL but n_src != n_units");
     if ((flags & TCW_ATOMIC_F32) && (flags & TCW_CLEAN)) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_ATOMIC_F32 has no fused clean_points");
+    if (flags & TCW_PACK) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_PACK belongs to tcw_workspace_bytes / tcw_forward_warp_pack");
     if ((flags & TCW_MASK_U8) && (flags & (TCW_CLEAN | TCW_ATOMIC_F32)))
         return fail(TCW_E_ARG, "tcw_forward_warp: TCW_MASK_U8 needs the default mode without TCW_CLEAN");
     const size_t hw = (size_t)h * w;
@@ -637,6 +657,7 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
     A.fused = 1; A.nv = 3; A.n_src = n_src; A.h = h; A.w = w;
     A.flow_out = out_flow;
     WinJob J;
+    memset(&J, 0, sizeof(J));
     J.n_units = n_units; J.flags = flags; J.out = (float*)out_frame; J.out_c = 3; J.out_mask = out_mask; J.out_depth = out_depth;
     J.is_image = 1; J.range_flag = range_flag;
     return window_enqueue(ctx, A, J, workspace, workspace_bytes, st);
@@ -712,6 +733,29 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     return TCW_OK;
 }
 
+// The warp and the resize + pack lines behind it, chunk by chunk (demo.py:77-100, 117-120).  Plain enqueue (no graph replay).
+TCW_API int tcw_forward_warp_pack(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                                  const int* src_index, const float* M, int n_units, int n_src, int H, int W, int h, int w,
+                                  int flags, float* out_video, float* out_masks, int* range_flag,
+                                  void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp_pack: ctx is NULL");
+    if (!frame || !depth || !M || !out_video || !out_masks) return fail(TCW_E_ARG, "tcw_forward_warp_pack: NULL buffer");
+    if (n_units <= 0 || n_src <= 0 || H <= 0 || W <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp_pack: bad shape");
+    if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp_pack: src_index is NULL but n_src != n_units");
+    if (flags & ~TCW_PER_UNIT_MAX) return fail(TCW_E_ARG, "tcw_forward_warp_pack: flags may only hold TCW_PER_UNIT_MAX");
+    if ((size_t)H * W >= 0x7fffffffull / 4 || (size_t)h * w >= (1u << 31)) return fail(TCW_E_ARG, "tcw_forward_warp_pack: image too large for this build");
+    WinArgs A;
+    memset(&A, 0, sizeof(A));
+    A.frame = frame; A.mask1 = mask1; A.depth = depth; A.src_index = src_index; A.Mall = M;
+    A.fused = 1; A.nv = 3; A.n_src = n_src; A.h = H; A.w = W;
+    A.flow_out = nullptr;                       // flow12 stays in the workspace
+    WinJob J;
+    memset(&J, 0, sizeof(J));
+    J.n_units = n_units; J.flags = flags | TCW_PACK; J.out_c = 3; J.is_image = 1; J.range_flag = range_flag;
+    J.pack_h = h; J.pack_w = w; J.pack_video = out_video; J.pack_masks = out_masks;
+    return window_enqueue(ctx, A, J, workspace, workspace_bytes, (cudaStream_t)cuda_stream);
+}
+
 TCW_API int tcw_project(tcw_ctx* ctx, const float* depth, const int* src_index, const float* M,
                         int n_units, int n_src, int h, int w, float* out_points, void* cuda_stream) {
     if (!ctx || !depth || !M || !out_points) return fail(TCW_E_ARG, "tcw_project: NULL argument");
@@ -738,6 +782,7 @@ TCW_API int tcw_splat(tcw_ctx* ctx, const float* frame, const float* mask1, cons
     A.frame = frame; A.mask1 = mask1; A.depth = depth; A.gflow = flow; A.gflow_mask = flow_mask;
     A.fused = 0; A.nv = c; A.n_src = b; A.h = h; A.w = w;
     WinJob J;
+    memset(&J, 0, sizeof(J));
     J.n_units = b; J.flags = flags & TCW_PER_UNIT_MAX; J.out = out; J.out_c = c; J.out_mask = out_mask; J.out_depth = nullptr;
     J.is_image = (flags & TCW_IS_IMAGE) ? 1 : 0; J.range_flag = range_flag;
     return window_enqueue(ctx, A, J, workspace, workspace_bytes, (cudaStream_t)cuda_stream);
@@ -762,7 +807,7 @@ TCW_API int tcw_resize_pack(tcw_ctx* ctx, const float* frame, const float* mask,
     const size_t want = (total + 255) / 256;
     const int blocks = (int)(want < (size_t)ctx->sm_count * 8 ? want : (size_t)ctx->sm_count * 8);
     k_resize_pack<<<blocks, 256, 0, (cudaStream_t)cuda_stream>>>(frame, mask, n, H, W, h, w, (float)H / (float)h, (float)W / (float)w,
-                                                               out_video, out_masks);
+                                                               out_video, out_masks, n, 0);
     LAUNCH_CHECK("k_resize_pack");
     return TCW_OK;
 }

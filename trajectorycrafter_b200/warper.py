@@ -392,6 +392,40 @@ class Warper:
         _lib.check(rc, "tcw_resize_pack")
         return video, cmask
 
+    def forward_warp_pack(self, frames, depths, transformation1, transformation2, intrinsic1, intrinsic2=None, sample_size=(384, 672),
+                          mask1=None, src_index=None, per_frame_max: bool = True, check_range=True):
+        """The reference's warp loop and the lines behind it in ONE submission (demo.py:77-100, 117-120): equal, bit for bit, to
+        ``pack_condition(*forward_warp_batch(...)[:2], sample_size)``, without the full-resolution colour / mask / depth / flow ever
+        being written out (``tcw_forward_warp_pack``).  Returns (cond_video (1,3,n,h,w), cond_masks (1,1,n,h,w)).
+        ``check_range`` as in ``forward_warp_matrices``."""
+        n_src, c, H, W = frames.shape
+        M = prepare_matrices(transformation1, transformation2, intrinsic1, intrinsic2)
+        n = M.shape[0]
+        assert c == 3 and depths.shape == (n_src, 1, H, W)
+        assert mask1 is None or mask1.shape == (n_src, 1, H, W)
+        if src_index is None:
+            assert n == n_src, "src_index is required when the number of poses differs from the number of frames"
+        elif not src_index.is_cuda:
+            assert src_index.shape == (n,) and int(src_index.min()) >= 0 and int(src_index.max()) < n_src, "src_index out of range"
+        h, w = int(sample_size[0]), int(sample_size[1])
+        frames_d, depths_d, mask1_d = self._dev(frames), self._dev(depths), self._dev(mask1)
+        M_d = M.to(self.device, torch.float32, non_blocking=True).contiguous()
+        si_d = None if src_index is None else src_index.to(self.device, torch.int32).contiguous()
+        flags = _lib.TCW_PER_UNIT_MAX if per_frame_max else 0
+        video = torch.empty((1, 3, n, h, w), dtype=torch.float32, device=self.device)
+        cmask = torch.empty((1, 1, n, h, w), dtype=torch.float32, device=self.device)
+        lazy_flag = isinstance(check_range, torch.Tensor)
+        flag = check_range if lazy_flag else (torch.zeros(1, dtype=torch.int32, device=self.device) if check_range else None)
+        ws = self._get_workspace(n, H, W, flags | _lib.TCW_PACK)
+        with torch.cuda.device(self.device):
+            rc = self._lib.tcw_forward_warp_pack(self._context(), _ptr(frames_d), _ptr(mask1_d), _ptr(depths_d), _ptr(si_d), _ptr(M_d),
+                                                 n, n_src, H, W, h, w, flags, _ptr(video), _ptr(cmask), _ptr(flag),
+                                                 _ptr(ws), ws.numel(), self._stream())
+        _lib.check(rc, "tcw_forward_warp_pack")
+        if flag is not None and not lazy_flag:
+            self.check_status(int(flag.item()))
+        return video, cmask
+
     def depth_postprocess(self, res, near: float = 0.0001, far: float = 10000.0, radius_scale: float = 1.0):
         """The lines that end the reference's depth stage (models/infer.py:79-92) plus the trajectory radius of
         demo.py:539-543, on the device: channel mean, min / max normalisation over the whole clip, ``* 3900``, floor at 1e-5,
