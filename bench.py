@@ -513,25 +513,33 @@ def run_ours(args):
     # kernel stores straight into rank 0's buffer through peer-mapped memory (no collective, no local copy)
     strong = with_gather = None
     if world > 1:
-        from trajectorycrafter_b200.sharding import (PeerBuffer, gather_packed, local_sources, packed_buffer, packed_views,
-                                                     shard_bounds, unpack_gathered)
+        from trajectorycrafter_b200.sharding import (PeerBuffer, balanced_units, gather_packed, packed_buffer, packed_views,
+                                                     sources_of, unpack_gathered)
         sf, sd, sM, ssrc = build_workload(1234)                       # the same clip on every rank
         n_all = sM.shape[0]
-        lo, hi = shard_bounds(n_all, world, rank)
-        nl = hi - lo
-        needed, lsrc = local_sources(ssrc, lo, hi)                    # a rank uploads only the source frames its units read
+        # a rank takes a block of frames of EVERY trajectory (the eight presets cost 0.43 - 0.78 ms per 49 units: one whole
+        # preset per rank leaves the step at the slowest one), and writes each unit to its slot of the clip (dst_index)
+        ids = balanced_units(n_all, N_FRAMES, world, rank)
+        order = torch.cat([balanced_units(n_all, N_FRAMES, world, r) for r in range(world)])      # unit held at each gathered position
+        nl = ids.numel()
+        assert all(balanced_units(n_all, N_FRAMES, world, r).numel() == nl for r in range(world))
+        needed, lsrc = sources_of(ssrc, ids)                          # a rank uploads only the source frames its units read
         sf_d, sd_d = sf[needed].contiguous().to(dev), sd[needed].contiguous().to(dev)
-        sM_d, ss_d = sM[lo:hi].contiguous().to(dev), lsrc.to(dev)
+        sM_d, ss_d, ids_d = sM[ids].contiguous().to(dev), lsrc.to(dev), ids.to(dev)
         o_depth, o_flow = torch.empty((nl, 1, H, W), device=dev), torch.empty((nl, 2, H, W), device=dev)
         o_col, o_msk = torch.empty((nl, 3, H, W), device=dev), torch.empty((nl, 1, H, W), device=dev)
+        a_depth, a_flow = torch.empty((n_all, 1, H, W), device=dev), torch.empty((n_all, 2, H, W), device=dev)   # scatter form: clip-sized
         packed = packed_buffer(nl, H, W, dev)
         p_col, p_msk = packed_views(packed, nl, H, W)
         peer = PeerBuffer(warper, n_all, H, W, dst=0)
-        r_col, r_msk = peer.views(lo, hi)
 
-        def warp_into(col, msk, u8):
-            warper.forward_warp_matrices(sf_d, sd_d, sM_d, src_index=ss_d, per_frame_max=True, check_range=flag,
-                                         out=(col, msk, o_depth, o_flow), mask_u8=u8)
+        def warp_into(col, msk, u8, scatter=False):
+            if scatter:      # every unit straight to its slot of the clip on rank 0; depth / flow12 stay local
+                warper.forward_warp_matrices(sf_d, sd_d, sM_d, src_index=ss_d, per_frame_max=True, check_range=flag,
+                                             out=(col, msk, a_depth, a_flow), mask_u8=u8, dst_index=ids_d)
+            else:
+                warper.forward_warp_matrices(sf_d, sd_d, sM_d, src_index=ss_d, per_frame_max=True, check_range=flag,
+                                             out=(col, msk, o_depth, o_flow), mask_u8=u8)
 
         def timed(fn, steps):
             for _ in range(3):
@@ -553,7 +561,7 @@ def run_ours(args):
             warp_into(p_col, p_msk, True)
             gathered[0] = gather_packed(packed, n_all, H, W, dst=0)
         ms_nccl = timed(nccl_step, ksteps)
-        ms_peer = timed(lambda: warp_into(r_col, r_msk, True), ksteps)
+        ms_peer = timed(lambda: warp_into(peer.colour, peer.mask, True, scatter=True), ksteps)
         # the assembled clip on rank 0 must equal what one GPU computes for the whole clip, bit for bit (fixed summation order)
         same = None
         if rank == 0:
@@ -561,21 +569,26 @@ def run_ours(args):
             ref_c, ref_m, _, _ = warper.forward_warp_matrices(sf.to(dev), sd.to(dev), sM[pick].to(dev), src_index=ssrc[pick].to(dev),
                                                               per_frame_max=True, check_range=flag, mask_u8=True)
             parts = unpack_gathered(gathered[0], n_all, H, W)
-            g_col = torch.cat([p_[0] for p_ in parts])[pick.to(dev)]
+            where = torch.empty(n_all, dtype=torch.int64)
+            where[order] = torch.arange(n_all)                       # gathered position of every unit (rank-major blocks)
+            g_col = torch.cat([p_[0] for p_ in parts])[where[pick].to(dev)]
             same = bool(torch.equal(peer.colour[pick.to(dev)], ref_c) and torch.equal(peer.mask[pick.to(dev)], ref_m)
                         and torch.equal(g_col, ref_c))
         wire = 13 * (n_all - n_all // world) * H * W
         px_all = n_all * H * W
         strong = {"value": px_all / (ms_strong * 1e-3) / 1e6, "unit": "Mpix/s", "ms": ms_strong, "units_per_rank": nl,
-                  "what": "config 2's 392 units of ONE clip sharded over the ranks, outputs left on each rank, no collective"}
+                  "what": "config 2's 392 units of ONE clip sharded over the ranks (a frame block of every trajectory per rank: "
+                          "sharding.balanced_units), outputs left on each rank, no collective"}
         with_gather = {"value": px_all / (ms_peer * 1e-3) / 1e6, "unit": "Mpix/s", "ms": ms_peer,
                        "ingress_GBps": wire / (ms_peer * 1e-3) / 1e9, "bytes_into_rank0": wire,
                        "nvlink_bound_ms": wire / 770e9 * 1e3,
-                       "how": "fused: the gather kernel of every rank stores colour f32 + mask u8 (13 B/px) straight into rank 0's "
-                              "buffer (CUDA IPC peer mapping over NVLink / NVSwitch); the step ends when all ranks' kernels have finished",
+                       "how": "fused: the gather kernel of every rank stores colour f32 + mask u8 (13 B/px) of each of its units straight "
+                              "into that unit's slot of rank 0's buffer (tcw_forward_warp_scatter over a CUDA IPC peer mapping, NVLink / "
+                              "NVSwitch); the step ends when all ranks' kernels have finished",
                        "nccl_single_gather": {"value": px_all / (ms_nccl * 1e-3) / 1e6, "ms": ms_nccl,
                                               "ingress_GBps": wire / (ms_nccl * 1e-3) / 1e9,
-                                              "how": "warp into a per-rank packed buffer, then ONE dist.gather of 13 B/px"},
+                                              "how": "warp into a per-rank packed buffer, then ONE dist.gather of 13 B/px (rank-major blocks: "
+                                                     "the clip order still needs a permutation on rank 0, not timed)"},
                        "assembled_equals_single_gpu_bits": same}
         if rank != 0:
             peer.close()          # unmap before the owner frees

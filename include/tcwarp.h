@@ -95,6 +95,19 @@ int tcw_forward_warp(tcw_ctx* ctx,
                      int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream);
 
 /*
+ * tcw_forward_warp with a destination index (multi-GPU sharding; the reference has one process and one loop,
+ * demo.py:77-90): unit u of this call writes unit slot dst_index[u] of out_frame / out_mask / out_depth / out_flow, which hold
+ * n_dst units.  A rank can then take ANY subset of a clip's units -- a few frames of every trajectory, so that all ranks cost the
+ * same -- and still store each result where it belongs in the assembled clip, in its own memory or (tcw_ipc_open) another GPU's.
+ * dst_index: n_units ints on the DEVICE, distinct, in [0, n_dst); an entry outside writes slot 0 and sets TCW_STATUS_SRC_INDEX.
+ * Default mode only (no TCW_CLEAN / TCW_ATOMIC_F32); TCW_MASK_U8 allowed.  Everything else as tcw_forward_warp.
+ */
+int tcw_forward_warp_scatter(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                             const int* src_index, const float* M, const int* dst_index, int n_units, int n_src, int n_dst,
+                             int h, int w, int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                             int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream);
+
+/*
  * Same operation with HOST buffers (pageable or pinned): uploads inputs, runs, downloads outputs,
  * pipelined over internal streams; synchronous on return.  M and src_index are host pointers here.
  * range_flag is a host int (written).  This is the call `bench.py` times as "e2e".

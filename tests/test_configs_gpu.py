@@ -262,3 +262,49 @@ def test_odd_sizes_vs_oracle(warper, shape, mode):
     got = warper.forward_warp_matrices(frames, depths, M, src_index=src, mask1=mask1, accumulation=mode)
     ref = oracle.forward_warp(frames, mask1, depths, M, src_index=src.numpy(), per_unit_max=True)
     check(got, ref, f"odd {h}x{w} {mode}")
+
+
+@pytest.mark.gpu
+def test_scatter_destinations_equal_the_direct_call():
+    """tcw_forward_warp_scatter (multi-GPU sharding by balanced unit subsets): a subset of units written to its slots of a
+    larger output equals the same units of one whole-clip call, bit for bit; the other slots are untouched; a bad
+    destination index is flagged, not written out of bounds."""
+    import torch
+    from trajectorycrafter_b200 import Warper, prepare_matrices
+    from trajectorycrafter_b200.sharding import balanced_units, sources_of
+    from trajectorycrafter_b200.workloads import orbit_units, synthetic_clip
+    nf, h, w = 7, 96, 160
+    frames, depths = synthetic_clip(nf, h, w, seed=5)
+    T1, T2, K, src = orbit_units(depths, h, w, presets=[(0, 30), (10, -45), (-20, 90)])
+    M = prepare_matrices(T1, T2, K)
+    n = M.shape[0]
+    wp = Warper(device="cuda:0")
+    f_d, d_d = frames.cuda(), depths.cuda()
+    ref = wp.forward_warp_matrices(f_d, d_d, M, src_index=src.cuda())
+    world = 3
+    outs = [torch.full((n, c, h, w), 7.0, device="cuda:0") for c in (3, 1, 1, 2)]
+    outs[1] = torch.full((n, 1, h, w), 7, dtype=torch.uint8, device="cuda:0")
+    for rank in range(world):
+        ids = balanced_units(n, nf, world, rank)
+        needed, lsrc = sources_of(src, ids)
+        # the rank holds only the source frames its units read
+        wp.forward_warp_matrices(f_d[needed.cuda()].contiguous(), d_d[needed.cuda()].contiguous(), M[ids], src_index=lsrc.cuda(),
+                                 out=tuple(outs), mask_u8=True, dst_index=ids.cuda())
+        done = torch.cat([balanced_units(n, nf, world, r) for r in range(rank + 1)]).cuda()
+        rest = torch.ones(n, dtype=torch.bool, device="cuda:0")
+        rest[done] = False
+        assert torch.equal(outs[0][done], ref[0][done]) and torch.equal(outs[1][done].float(), ref[1][done])
+        assert torch.equal(outs[2][done], ref[2][done]) and torch.equal(outs[3][done], ref[3][done])
+        assert bool((outs[0][rest] == 7.0).all()) and bool((outs[1][rest] == 7).all())
+    # float mask, no depth / flow outputs, host index vector
+    o2 = (torch.zeros((n, 3, h, w), device="cuda:0"), torch.zeros((n, 1, h, w), device="cuda:0"), None, None)
+    ids = balanced_units(n, nf, world, 1)
+    wp.forward_warp_matrices(f_d, d_d, M[ids], src_index=src[ids], out=o2, dst_index=ids)
+    assert torch.equal(o2[0][ids.cuda()], ref[0][ids.cuda()]) and torch.equal(o2[1][ids.cuda()], ref[1][ids.cuda()])
+    # a destination outside the outputs: flagged (IndexError through the status word), nothing written past the tensors
+    bad = ids.clone().cuda()
+    bad[0] = n + 5
+    with pytest.raises(IndexError):
+        wp.forward_warp_matrices(f_d, d_d, M[ids], src_index=src[ids].cuda(), out=o2, dst_index=bad)
+    with pytest.raises(AssertionError):
+        wp.forward_warp_matrices(f_d, d_d, M[ids], src_index=src[ids], out=o2, dst_index=torch.zeros_like(ids))

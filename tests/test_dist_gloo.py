@@ -98,3 +98,24 @@ def test_single_gather_of_packed_colour_and_u8_mask():
         assert p.exitcode == 0
     status, shape = q.get()
     assert status == "ok"
+
+
+def test_balanced_units_partition_the_clip():
+    """Every unit belongs to exactly one rank; with rotation 8 groups of 49 give 49 units to each of 8 ranks, and every rank
+    holds a block of every group."""
+    import torch
+    from trajectorycrafter_b200.sharding import balanced_units, sources_of
+    for n, gs, world in ((392, 49, 8), (392, 49, 4), (392, 49, 2), (100, 49, 3), (7, 49, 8), (49, 49, 1)):
+        parts = [balanced_units(n, gs, world, r) for r in range(world)]
+        allu = torch.cat(parts)
+        assert allu.numel() == n and torch.equal(torch.sort(allu).values, torch.arange(n))
+        for p in parts:
+            assert torch.equal(p, torch.sort(p).values)
+    parts = [balanced_units(392, 49, 8, r) for r in range(8)]
+    assert all(p.numel() == 49 for p in parts)
+    assert all(len(set((p // 49).tolist())) == 8 for p in parts)
+    sizes = [balanced_units(392, 49, 8, r, rotate=False).numel() for r in range(8)]
+    assert max(sizes) == 56 and min(sizes) == 48      # why the blocks rotate
+    src = torch.arange(392) % 49
+    needed, local = sources_of(src, parts[3])
+    assert torch.equal(needed[local.long()], src[parts[3]])

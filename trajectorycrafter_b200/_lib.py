@@ -38,6 +38,8 @@ SIGNATURES = {
     "tcw_workspace_bytes": (c_int, [c_void_p, c_int, c_int, c_int, c_int, POINTER(c_size_t)]),
     "tcw_forward_warp": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int,
                                  _VP, _VP, _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
+    "tcw_forward_warp_scatter": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, _IP, c_int, c_int, c_int, c_int, c_int, c_int,
+                                         _VP, _VP, _FP, _FP, _IP, _VP, c_size_t, c_void_p]),
     "tcw_forward_warp_host": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int,
                                       _VP, _VP, _FP, _FP, POINTER(c_int)]),
     "tcw_forward_warp_pack": (c_int, [c_void_p, _FP, _FP, _FP, _IP, _FP, c_int, c_int, c_int, c_int, c_int, c_int, c_int,

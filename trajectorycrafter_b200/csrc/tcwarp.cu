@@ -52,7 +52,8 @@ struct tcw_ctx {
     struct GraphKey {
         const void *frame, *mask1, *depth, *src_index, *M, *out_frame, *out_mask, *out_depth, *out_flow, *range_flag, *workspace;
         size_t workspace_bytes;
-        int n_units, n_src, h, w, flags;
+        const void* dst_index;
+        int n_units, n_src, h, w, flags, n_dst;
     } last_key, graph_key;
     int last_key_valid;
     cudaGraphExec_t graph_exec;
@@ -506,8 +507,12 @@ static int window_enqueue(tcw_ctx* ctx, WinArgs A, const WinJob& J, void* worksp
             N.out_frame = J.out; N.out_mask = (float*)J.out_mask;
         }
         prof_begin(ctx, PK_NORMALISE, nu, sk);
-        if (N.out_c == 3 && N.is_image && N.out_depth) k_gather_normalise<true><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
-        else k_gather_normalise<false><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
+        const bool img3 = N.out_c == 3 && N.is_image && N.out_depth;
+        if (A.dst_index) {
+            if (img3) k_gather_normalise<true, true><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
+            else k_gather_normalise<false, true><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
+        } else if (img3) k_gather_normalise<true, false><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
+        else k_gather_normalise<false, false><<<dim3(g3.x, nu), 128, 0, sk>>>(A, N, u0, prep0, slot0, tiles_x);
         prof_end(ctx, sk);
         LAUNCH_CHECK("k_gather_normalise");
         if (clean) {
@@ -633,13 +638,16 @@ static int atomic_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, 
 static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
                                 const int* src_index, const float* M, int n_units, int n_src, int h, int w,
                                 int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
-                                int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+                                int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream,
+                                const int* dst_index = nullptr, int n_dst = 0) {
     if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp: ctx is NULL");
     if (!frame || !depth || !M || !out_frame || !out_mask) return fail(TCW_E_ARG, "tcw_forward_warp: NULL buffer");
     if (n_units <= 0 || n_src <= 0 || h <= 0 || w <= 0) return fail(TCW_E_ARG, "tcw_forward_warp: bad shape");
     if (!src_index && n_src != n_units) return fail(TCW_E_ARG, "tcw_forward_warp: src_index is NULL but n_src != n_units");
     if ((flags & TCW_ATOMIC_F32) && (flags & TCW_CLEAN)) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_ATOMIC_F32 has no fused clean_points");
     if (flags & TCW_PACK) return fail(TCW_E_ARG, "tcw_forward_warp: TCW_PACK belongs to tcw_workspace_bytes / tcw_forward_warp_pack");
+    if (dst_index && (flags & (TCW_CLEAN | TCW_ATOMIC_F32))) return fail(TCW_E_ARG, "tcw_forward_warp_scatter: default mode without TCW_CLEAN only");
+    if (dst_index && n_dst <= 0) return fail(TCW_E_ARG, "tcw_forward_warp_scatter: n_dst must be positive");
     if ((flags & TCW_MASK_U8) && (flags & (TCW_CLEAN | TCW_ATOMIC_F32)))
         return fail(TCW_E_ARG, "tcw_forward_warp: TCW_MASK_U8 needs the default mode without TCW_CLEAN");
     const size_t hw = (size_t)h * w;
@@ -656,6 +664,7 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
     A.frame = frame; A.mask1 = mask1; A.depth = depth; A.src_index = src_index; A.Mall = M;
     A.fused = 1; A.nv = 3; A.n_src = n_src; A.h = h; A.w = w;
     A.flow_out = out_flow;
+    A.dst_index = dst_index; A.n_dst = n_dst;
     WinJob J;
     memset(&J, 0, sizeof(J));
     J.n_units = n_units; J.flags = flags; J.out = (float*)out_frame; J.out_c = 3; J.out_mask = out_mask; J.out_depth = out_depth;
@@ -667,10 +676,11 @@ static int forward_warp_enqueue(tcw_ctx* ctx, const float* frame, const float* m
 // launches on four streams; enqueueing them costs the host about as long as the GPU needs to run them, so a call
 // whose arguments equal those of the call before is captured once and replayed afterwards.  Kernels read the
 // matrices, indices and images through the pointers at run time, so new CONTENTS need no new graph.
-TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
-                             const int* src_index, const float* M, int n_units, int n_src, int h, int w,
-                             int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
-                             int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+static int forward_warp_entry(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                              const int* src_index, const float* M, int n_units, int n_src, int h, int w,
+                              int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                              int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream,
+                              const int* dst_index, int n_dst) {
     if (!ctx) return fail(TCW_E_ARG, "tcw_forward_warp: ctx is NULL");
     cudaStream_t st = (cudaStream_t)cuda_stream;
     bool eligible = !ctx->graphs_off && !ctx->prof_on;
@@ -680,13 +690,13 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     }
     if (!eligible)
         return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
-                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream, dst_index, n_dst);
     tcw_ctx::GraphKey key;
     memset(&key, 0, sizeof(key));
     key.frame = frame; key.mask1 = mask1; key.depth = depth; key.src_index = src_index; key.M = M;
     key.out_frame = out_frame; key.out_mask = out_mask; key.out_depth = out_depth; key.out_flow = out_flow;
     key.range_flag = range_flag; key.workspace = workspace; key.workspace_bytes = workspace_bytes;
-    key.n_units = n_units; key.n_src = n_src; key.h = h; key.w = w; key.flags = flags;
+    key.n_units = n_units; key.n_src = n_src; key.h = h; key.w = w; key.flags = flags; key.dst_index = dst_index; key.n_dst = n_dst;
     if (ctx->graph_exec && !memcmp(&key, &ctx->graph_key, sizeof(key))) {
         CUDA_TRY(cudaGraphLaunch(ctx->graph_exec, st));
         ctx->launches += ctx->graph_launches;
@@ -697,14 +707,14 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
     ctx->last_key_valid = 1;
     if (!repeat)      // first sight of these arguments: plain enqueue (a caller that allocates fresh outputs never repeats)
         return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
-                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream, dst_index, n_dst);
     // second identical call in a row: capture it on an internal stream, instantiate, launch on the caller's stream
     if (!ctx->s_cap) CUDA_TRY(cudaStreamCreateWithFlags(&ctx->s_cap, cudaStreamNonBlocking));
     if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
     const long long before = ctx->launches;
     CUDA_TRY(cudaStreamBeginCapture(ctx->s_cap, cudaStreamCaptureModeThreadLocal));
     const int rc = forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
-                                        out_depth, out_flow, range_flag, workspace, workspace_bytes, ctx->s_cap);
+                                        out_depth, out_flow, range_flag, workspace, workspace_bytes, ctx->s_cap, dst_index, n_dst);
     cudaGraph_t graph = nullptr;
     const cudaError_t ce = cudaStreamEndCapture(ctx->s_cap, &graph);
     ctx->graph_launches = ctx->launches - before;
@@ -715,7 +725,7 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         ctx->graphs_off = 1;      // do not try again in this context; fall back to plain enqueue
         if (rc) return rc;
         return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
-                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream, dst_index, n_dst);
     }
     cudaError_t ie = cudaGraphInstantiate(&ctx->graph_exec, graph, 0);
     if (ie == cudaSuccess) ie = cudaGraphUpload(ctx->graph_exec, st);      // pre-pay the first-launch upload
@@ -725,12 +735,32 @@ TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask
         if (ctx->graph_exec) { cudaGraphExecDestroy(ctx->graph_exec); ctx->graph_exec = nullptr; }
         ctx->graphs_off = 1;
         return forward_warp_enqueue(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask,
-                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream);
+                                    out_depth, out_flow, range_flag, workspace, workspace_bytes, cuda_stream, dst_index, n_dst);
     }
     ctx->graph_key = key;
     CUDA_TRY(cudaGraphLaunch(ctx->graph_exec, st));
     ctx->launches += ctx->graph_launches;
     return TCW_OK;
+}
+
+TCW_API int tcw_forward_warp(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                             const int* src_index, const float* M, int n_units, int n_src, int h, int w,
+                             int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                             int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    return forward_warp_entry(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask, out_depth,
+                              out_flow, range_flag, workspace, workspace_bytes, cuda_stream, nullptr, 0);
+}
+
+// tcw_forward_warp whose unit u writes unit slot dst_index[u] of output tensors that hold n_dst units: a rank of a multi-GPU job
+// can take ANY subset of a clip's units (e.g. a few frames of every trajectory, so that all ranks cost the same) and still store
+// each result where it belongs in the assembled clip -- its own or, through tcw_ipc_open, another GPU's memory.
+TCW_API int tcw_forward_warp_scatter(tcw_ctx* ctx, const float* frame, const float* mask1, const float* depth,
+                                     const int* src_index, const float* M, const int* dst_index, int n_units, int n_src, int n_dst,
+                                     int h, int w, int flags, void* out_frame, void* out_mask, float* out_depth, float* out_flow,
+                                     int* range_flag, void* workspace, size_t workspace_bytes, void* cuda_stream) {
+    if (!dst_index) return fail(TCW_E_ARG, "tcw_forward_warp_scatter: dst_index is NULL");
+    return forward_warp_entry(ctx, frame, mask1, depth, src_index, M, n_units, n_src, h, w, flags, out_frame, out_mask, out_depth,
+                              out_flow, range_flag, workspace, workspace_bytes, cuda_stream, dst_index, n_dst);
 }
 
 // The warp and the resize + pack lines behind it, chunk by chunk (demo.py:77-100, 117-120).  Plain enqueue (no graph replay).

@@ -66,7 +66,17 @@ struct WinArgs {
     float4* pool4; float* poolw; long long pool_cells; int n_slots;
     float4* spill4; float* spillw;
     int* status;                                             // device word: bit 1 = a footprint was reduced into the shared plane, bit 2 = src_index out of range
+    // tcw_forward_warp_scatter: unit u's results go to unit slot dst_index[u] of the (n_dst, ...) output tensors (nullptr: slot u)
+    const int* dst_index; int n_dst;
 };
+
+// output slot of unit u (an index outside [0, n_dst) writes slot 0 and is flagged: never write out of bounds)
+__device__ __forceinline__ int win_dst(const WinArgs& A, int u) {
+    if (!A.dst_index) return u;
+    int d = A.dst_index[u];
+    if ((unsigned)d >= (unsigned)A.n_dst) { if (A.status) atomicOr(A.status, 4); d = 0; }
+    return d;
+}
 
 __device__ __forceinline__ int win_src(const WinArgs& A, int u) {
     int s = A.src_index ? A.src_index[u] : u;
@@ -117,7 +127,7 @@ k_win_prepass(WinArgs A, int unit0, int prep0, int slot0) {
         u64 u0p = 0;
         float a0A = 0.f, a1A = 0.f, a2A = 0.f, a0B = 0.f, a1B = 0.f, a2B = 0.f;
         if (PROJECT) {
-            flp = A.flow_out ? A.flow_out + (size_t)u * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
+            flp = A.flow_out ? A.flow_out + (size_t)win_dst(A, u) * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
             zp = A.zbuf + (size_t)ps * hw;
             const float* __restrict__ Mu = A.Mall + (size_t)u * M_FLOATS;
             #pragma unroll
@@ -690,7 +700,7 @@ k_splat_window(WinArgs A, int unit0, int prep0, int slot0) {
     WinSrc S;
     if (FUSED) {
         const int s = win_src(A, u);
-        S.fl = A.flow_out ? A.flow_out + (size_t)u * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
+        S.fl = A.flow_out ? A.flow_out + (size_t)win_dst(A, u) * 2 * hw : A.flowbuf + (size_t)ps * 2 * hw;
         S.wd = A.zbuf + (size_t)ps * hw;
         S.v[0] = A.frame + (size_t)s * 3 * hw; S.v[1] = S.v[0] + hw; S.v[2] = S.v[1] + hw; S.v[3] = nullptr;
         S.m1 = A.mask1 ? A.mask1 + (size_t)s * hw : nullptr; S.fm = nullptr;
@@ -865,7 +875,7 @@ struct WinNormArgs {
 
 // IMG3: the forward warp's own shape -- three colour planes (holes -1, range check, clamp) and a depth plane -- with the
 // branches of the generic store loop resolved at compile time and 32-bit byte offsets from one uniform base per output.
-template <bool IMG3>
+template <bool IMG3, bool SCATTER>      // SCATTER: tcw_forward_warp_scatter (its own instantiation: the default one stays as it was)
 __global__ void __launch_bounds__(128)
 k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, int tiles_x) {
     constexpr unsigned FULL = 0xffffffffu;
@@ -995,9 +1005,10 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
     if (IMG3) {
         if (tx < w && row0 < h) {
             // byte offsets fit 32 bits: 3 * h * w * 4 < 2^32 (h * w < 2^28 is checked at submission)
-            char* __restrict__ fb = (char*)(N.out_frame + (size_t)u * 3 * hw);
-            char* __restrict__ db = (char*)(N.out_depth + (size_t)u * hw);
-            char* __restrict__ mb = (char*)N.out_mask + (size_t)u * hw * (N.mask_u8 ? 1 : 4);
+            const int uo = SCATTER ? win_dst(A, u) : u;
+            char* __restrict__ fb = (char*)(N.out_frame + (size_t)uo * 3 * hw);
+            char* __restrict__ db = (char*)(N.out_depth + (size_t)uo * hw);
+            char* __restrict__ mb = (char*)N.out_mask + (size_t)uo * hw * (N.mask_u8 ? 1 : 4);
             const unsigned hw4 = (unsigned)hw * 4u, w4 = (unsigned)w * 4u;
             unsigned off = ((unsigned)row0 * (unsigned)w + (unsigned)tx) * 4u;
             const int nr = R1 - row0;
@@ -1021,10 +1032,11 @@ k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, in
         }
     } else if (tx < w && row0 < h) {
         const size_t p0 = (size_t)row0 * w + tx;
-        float* o0 = N.out_frame + (size_t)u * N.out_c * hw + p0;
-        float* om = N.out_mask + (size_t)u * hw + p0;
-        unsigned char* om8 = (unsigned char*)N.out_mask + (size_t)u * hw + p0;
-        float* od = N.out_depth ? N.out_depth + (size_t)u * hw + p0 : nullptr;
+        const int uo = SCATTER ? win_dst(A, u) : u;
+        float* o0 = N.out_frame + (size_t)uo * N.out_c * hw + p0;
+        float* om = N.out_mask + (size_t)uo * hw + p0;
+        unsigned char* om8 = (unsigned char*)N.out_mask + (size_t)uo * hw + p0;
+        float* od = N.out_depth ? N.out_depth + (size_t)uo * hw + p0 : nullptr;
         const float hole = N.is_image ? -1.0f : 0.0f;
         #pragma unroll
         for (int r = 0; r < 8; ++r) {

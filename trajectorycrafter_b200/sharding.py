@@ -26,6 +26,27 @@ def shard_counts(n_units: int, world_size: int) -> List[int]:
             for r in range(world_size)]
 
 
+def balanced_units(n_units: int, group_size: int, world_size: int, rank: int, rotate: bool = True) -> torch.Tensor:
+    """Unit ids (ascending, int64) of `rank` when every GROUP of `group_size` consecutive units (one trajectory of a clip:
+    the units of one camera path cost alike, different paths do not -- a +-90 degree orbit costs 1.8x a small one) is cut
+    into `world_size` contiguous frame blocks and rank r takes one block of EVERY group.  With `rotate` the block taken from
+    group g is block (r + g) mod world, so the ragged remainders even out (8 groups of 49 on 8 ranks: 49 units each).
+    A trailing partial group is cut the same way.  To be used with ``forward_warp_matrices(..., dst_index=ids, out=...)``."""
+    assert 0 <= rank < world_size and n_units >= 0 and group_size > 0
+    ids = []
+    for g, g0 in enumerate(range(0, n_units, group_size)):
+        gs = min(group_size, n_units - g0)
+        lo, hi = shard_bounds(gs, world_size, (rank + g) % world_size if rotate else rank)
+        ids.append(torch.arange(g0 + lo, g0 + hi, dtype=torch.int64))
+    return torch.cat(ids) if ids else torch.zeros(0, dtype=torch.int64)
+
+
+def sources_of(src_index: torch.Tensor, unit_ids: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """``local_sources`` for an arbitrary unit subset: (needed source frames (k,), src_index of the subset remapped onto them)."""
+    needed, inverse = torch.unique(src_index[unit_ids].to(torch.int64), sorted=True, return_inverse=True)
+    return needed, inverse.to(torch.int32)
+
+
 def local_sources(src_index: torch.Tensor, lo: int, hi: int) -> Tuple[torch.Tensor, torch.Tensor]:
     """Source frames a rank needs for its unit block, and the block's src_index remapped onto them.
 

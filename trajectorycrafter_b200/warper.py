@@ -123,14 +123,16 @@ class Warper:
                               mask1: Optional[torch.Tensor] = None, src_index: Optional[torch.Tensor] = None,
                               per_frame_max: bool = True, mask: bool = False,
                               return_depth: bool = True, return_flow: bool = True, check_range=True,
-                              accumulation: str = "window", out=None, mask_u8: bool = False):
+                              accumulation: str = "window", out=None, mask_u8: bool = False, dst_index=None):
         """``forward_warp_batch`` on an already prepared (n_units,30) matrix block
         (``prepare_matrices``): [K1^-1 | rows 0..2 of T2*T1^-1 | K2] per unit.
 
         ``check_range`` True: raise AssertionError like the reference if a colour left [-1.1,1.1]
         (one host sync); False: skip; an int32 CUDA tensor: OR the flag into it, no sync (check it
         later).  ``out`` may carry preallocated (frame, mask, depth|None, flow|None) CUDA tensors -- they may live in a peer
-        GPU's memory (``sharding.PeerBuffer``).  ``mask_u8``: the validity mask is written as uint8 (default mode only)."""
+        GPU's memory (``sharding.PeerBuffer``).  ``mask_u8``: the validity mask is written as uint8 (default mode only).
+        ``dst_index`` (n_units,) int tensor: unit u is written to unit slot ``dst_index[u]`` of the ``out`` tensors, which then hold
+        ``out[0].shape[0]`` >= n units (``tcw_forward_warp_scatter``; default accumulation, ``mask=False``, ``out`` required)."""
         n_src, c, h, w = frames.shape
         n = M.shape[0]
         assert c == 3 and depths.shape == (n_src, 1, h, w) and M.shape == (n, 30)
@@ -155,12 +157,22 @@ class Warper:
         odt = torch.float64 if mask else torch.float32
         mdt = torch.uint8 if mask_u8 else odt
         assert not (mask_u8 and (mask or mode)), "mask_u8 needs the default accumulation and mask=False"
+        n_dst = n                      # units the output tensors hold
+        di_d = None
+        if dst_index is not None:
+            assert out is not None and not mask and not mode, "dst_index needs preallocated outputs, the default accumulation and mask=False"
+            assert dst_index.shape == (n,)
+            n_dst = out[0].shape[0]
+            if not dst_index.is_cuda:      # (a CUDA index vector is checked by the kernels: TCW_STATUS_SRC_INDEX)
+                assert int(dst_index.min()) >= 0 and int(dst_index.max()) < n_dst and len(set(dst_index.tolist())) == n, \
+                    "dst_index must hold distinct unit slots of the outputs"
+            di_d = dst_index.to(self.device, torch.int32).contiguous()
         if out is not None:
             out_frame, out_mask, out_depth, out_flow = out
-            assert out_frame.shape == (n, 3, h, w) and out_frame.dtype == odt and out_frame.is_contiguous()
-            assert out_mask.shape == (n, 1, h, w) and out_mask.dtype == mdt and out_mask.is_contiguous()
-            assert out_depth is None or (out_depth.shape == (n, 1, h, w) and out_depth.is_contiguous())
-            assert out_flow is None or (out_flow.shape == (n, 2, h, w) and out_flow.is_contiguous())
+            assert out_frame.shape == (n_dst, 3, h, w) and out_frame.dtype == odt and out_frame.is_contiguous()
+            assert out_mask.shape == (n_dst, 1, h, w) and out_mask.dtype == mdt and out_mask.is_contiguous()
+            assert out_depth is None or (out_depth.shape == (n_dst, 1, h, w) and out_depth.is_contiguous())
+            assert out_flow is None or (out_flow.shape == (n_dst, 2, h, w) and out_flow.is_contiguous())
         else:
             out_frame = torch.empty((n, 3, h, w), dtype=odt, device=self.device)
             out_mask = torch.empty((n, 1, h, w), dtype=mdt, device=self.device)
@@ -174,10 +186,16 @@ class Warper:
             flag = torch.zeros(1, dtype=torch.int32, device=self.device) if check_range else None
         ws = self._get_workspace(n, h, w, flags)
         with torch.cuda.device(self.device):
-            rc = self._lib.tcw_forward_warp(self._context(), _ptr(frames_d), _ptr(mask1_d), _ptr(depths_d),
-                                            _ptr(si_d), _ptr(M_d), n, n_src, h, w, flags,
-                                            _ptr(out_frame), _ptr(out_mask), _ptr(out_depth), _ptr(out_flow),
-                                            _ptr(flag), _ptr(ws), ws.numel(), self._stream())
+            if di_d is None:
+                rc = self._lib.tcw_forward_warp(self._context(), _ptr(frames_d), _ptr(mask1_d), _ptr(depths_d),
+                                                _ptr(si_d), _ptr(M_d), n, n_src, h, w, flags,
+                                                _ptr(out_frame), _ptr(out_mask), _ptr(out_depth), _ptr(out_flow),
+                                                _ptr(flag), _ptr(ws), ws.numel(), self._stream())
+            else:
+                rc = self._lib.tcw_forward_warp_scatter(self._context(), _ptr(frames_d), _ptr(mask1_d), _ptr(depths_d),
+                                                        _ptr(si_d), _ptr(M_d), _ptr(di_d), n, n_src, n_dst, h, w, flags,
+                                                        _ptr(out_frame), _ptr(out_mask), _ptr(out_depth), _ptr(out_flow),
+                                                        _ptr(flag), _ptr(ws), ws.numel(), self._stream())
         _lib.check(rc, "tcw_forward_warp")
         if flag is not None and not lazy_flag:
             self.check_status(int(flag.item()))
@@ -187,7 +205,7 @@ class Warper:
     def check_status(status: int) -> None:
         """Raise for the status bits a call ORs into its flag word (include/tcwarp.h TCW_STATUS_*)."""
         if status & _lib.TCW_STATUS_SRC_INDEX:
-            raise IndexError("src_index holds a value outside [0, n_src)")
+            raise IndexError("src_index holds a value outside [0, n_src) (or dst_index one outside the output tensors)")
         if status & _lib.TCW_STATUS_BOUNDS:      # only a -DTCW_BOUNDS_CHECK=1 build can raise it
             raise RuntimeError("bounds-checked build: a window / slab access left its allocation")
         # the reference asserts -1.1 <= warped <= 1.1 before clipping (models/utils.py:580-581)
