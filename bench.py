@@ -675,6 +675,14 @@ def run_ours(args):
         extras["twice"] = {"ms_per_frame": t_ms, "Mpix_per_s": H * W / (t_ms * 1e-3) / 1e6,
                            "what": "Warper.forward_warp(twice=True), b = 1, 384x672: forward colour + depth splat, flow splat, two backward "
                                    "splats, incl. the host-side matrix preparation of each call"}
+        # the same as ONE call with b = 49 (one trajectory; the reference's call-wide normaliser): 4 splats of 49 units + a projection
+        bT1, bT2, bK, _ = _ou(depths, H, W, presets=[(0, 12)])
+        tb_ms = dev_time(lambda: warper.forward_warp(frames_d, None, depths_d, bT1, bT2, bK, None, twice=True), 5)
+        tb_bytes = N_FRAMES * H * W * (44 + 36 + 44 + 28)      # colour+depth warp 44, flow splat (2 ch) 36, colour back-splat 44, depth back-splat 28 B/px
+        extras["twice_b49"] = {"ms": tb_ms, "Mpix_per_s": N_FRAMES * H * W / (tb_ms * 1e-3) / 1e6,
+                               "algorithmic_bytes": tb_bytes, "frac_of_hbm_peak": tb_bytes / (tb_ms * 1e-3) / 1e9 / peak,
+                               "what": "Warper.forward_warp(twice=True) with b = 49 at 384x672 in one call: forward warp, flow splat, two backward "
+                                       "splats on the window kernels (fixed summation order), plus the torch negation of the warped flow"}
         # N2: z-buffer renderer, 1 M points -> 576x1024 (point_size 2: nine footprint entries per point)
         pc = GlobalPointCloudWarper(device=f"cuda:{local}")
         g = torch.Generator().manual_seed(9)

@@ -308,3 +308,29 @@ def test_scatter_destinations_equal_the_direct_call():
         wp.forward_warp_matrices(f_d, d_d, M[ids], src_index=src[ids].cuda(), out=o2, dst_index=bad)
     with pytest.raises(AssertionError):
         wp.forward_warp_matrices(f_d, d_d, M[ids], src_index=src[ids], out=o2, dst_index=torch.zeros_like(ids))
+
+
+@pytest.mark.gpu
+def test_twice_batched_call(warper):
+    """forward_warp(twice=True) with b = 3 (one reference call with a batch: call-wide soft-z normaliser in every one of the
+    five splats, models/utils.py:296-347, :492) against the oracle chain."""
+    from trajectorycrafter_b200.workloads import synthetic_clip
+    h, w = 96, 160
+    frames, depths = synthetic_clip(3, h, w, seed=9)
+    T1, T2, K, _ = orbit_units(depths, h, w, presets=[(0, 12)])
+    got = warper.forward_warp(frames, None, depths, T1, T2, K, None, mask=False, twice=True)
+    M = prepare_matrices(T1, T2, K)
+    f1, m1, d1, fl, _ = oracle.forward_warp(frames, None, depths, M, per_unit_max=False)
+    zt = np.ascontiguousarray(oracle.project(depths, M)[..., 2])
+    wfl, _, _ = oracle.splat(fl, np.ones_like(m1), zt, fl, None, is_image=False)
+    tf, tm, _ = oracle.splat(f1, m1, np.ascontiguousarray(d1[:, 0]), -wfl, None, is_image=True)
+    td, _, _ = oracle.splat(d1, m1, np.ascontiguousarray(d1[:, 0]), -wfl, None, is_image=False)
+    gf, gm, gd = npy(got[0]), npy(got[1]), npy(got[2])
+    assert gf.shape == (3, 3, h, w) and got[3] is None
+    mism = int((gm != tm).sum())
+    agree = np.broadcast_to(gm == tm, tf.shape)
+    err = np.abs(gf.astype(np.float64) - tf)[agree].max()
+    print(f"twice, b = 3 at {h}x{w}: mask mismatches {mism} of {gm.size}, colour max |d| where masks agree {err:.3e}")
+    assert mism <= 2 and err <= 2e-5
+    valid = (gm > 0) & (tm > 0)
+    assert (np.abs(gd - td)[valid] <= 2e-5 * np.abs(td[valid])).all()
