@@ -340,8 +340,28 @@ static void lanes_plan(const tcw_ctx* ctx, int n_units, size_t hw, size_t bytes_
     if (g2 > per_lane) g2 = per_lane;
     *lanes = NL; *chunk = g2;
 }
+// The window path's schedule shape (profiles/r2_schedule_sweep.txt, second table): what pays is full launches and enough
+// rounds per lane to hide the tails, not L2 residency of the slabs -- 392 units at 384x672: 4 x 2 4.58 ms, 4 x 12 3.70, plateau
+// 3.65 - 3.70 from 12 units per launch on; 196 units: 4 x 7 1.82 (4 x 2 2.10); 98 and 49 units: 4 x 2..3 is the optimum.
+// Rule: four lanes, about eight rounds per lane, at least two units per launch, at most ~3.7 Mpixel per launch (beyond that a
+// launch is many waves anyway: one 1080p unit is eight 384x672 units' worth of CTAs).
+static void window_plan(const tcw_ctx* ctx, int n_units, size_t hw, int* lanes, int* chunk) {
+    int NL = ctx->lanes > 0 ? ctx->lanes : 4;
+    if (NL > 8) NL = 8;
+    if (NL > n_units) NL = n_units;
+    int g2 = ctx->chunk_units_override;
+    if (g2 <= 0) {
+        const int cap = (int)(3700000 / hw) > 1 ? (int)(3700000 / hw) : 1;
+        g2 = n_units / (NL * 8);
+        if (g2 < 2) g2 = 2;
+        if (g2 > cap) g2 = cap;
+    }
+    const int per_lane = (n_units + NL - 1) / NL;
+    if (g2 > per_lane) g2 = per_lane;
+    if (g2 < 1) g2 = 1;
+    *lanes = NL; *chunk = g2;
+}
 constexpr size_t ATOMIC_BYTES_PER_PX = NCH * sizeof(float);
-constexpr size_t WINDOW_BYTES_PER_PX = 32;      // slabs ~1.3 x 20 B + z' 4 B, written and read once more inside a chunk
 
 static int check_launch(tcw_ctx* ctx, const char* what) {
     ctx->launches++;
@@ -375,7 +395,7 @@ struct WinLayout {
 };
 static void win_layout(const tcw_ctx* ctx, int n_units, int h, int w, int flags, WinLayout* L) {
     const size_t hw = (size_t)h * w;
-    lanes_plan(ctx, n_units, hw, WINDOW_BYTES_PER_PX, &L->NL, &L->g2);
+    window_plan(ctx, n_units, hw, &L->NL, &L->g2);
     L->S = L->NL * L->g2;
     L->P = (flags & TCW_PER_UNIT_MAX) ? L->S : n_units;      // a call-wide normaliser needs every unit's pre-pass first
     L->strips_x = (w + 63) / 64;
