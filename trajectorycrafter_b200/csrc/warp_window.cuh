@@ -876,7 +876,9 @@ struct WinNormArgs {
 // IMG3: the forward warp's own shape -- three colour planes (holes -1, range check, clamp) and a depth plane -- with the
 // branches of the generic store loop resolved at compile time and 32-bit byte offsets from one uniform base per output.
 template <bool IMG3, bool SCATTER>      // SCATTER: tcw_forward_warp_scatter (its own instantiation: the default one stays as it was)
-__global__ void __launch_bounds__(128)
+// (8 CTAs per SM = 64 registers, 32 warps: in the 12-unit launches of the timed schedule the slabs come from HBM and the kernel is
+// latency-bound: 3.72 -> 3.60 ms per step; 10 CTAs spill: 4.04)
+__global__ void __launch_bounds__(128, 8)
 k_gather_normalise(WinArgs A, WinNormArgs N, int unit0, int prep0, int slot0, int tiles_x) {
     constexpr unsigned FULL = 0xffffffffu;
     __shared__ int4 cand_all[4][WIN_MAXC];                          // per warp: {x0, y0, bw | bh << 16, slab offset}
