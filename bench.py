@@ -31,10 +31,10 @@ N_FRAMES, H, W = 49, 384, 672
 # (profiles/), for the 24-unit launch shape the roofline figure is quoted on
 # dram__bytes_read.sum + dram__bytes_write.sum of one launch of the dominant kernel (ncu --set full, profiles/)
 NCU_TRAFFIC_BYTES_PER_LAUNCH = {"atomic": 238_216_960,   # r1_final_kernels_full_24units_ncu.txt: k_splat_pair, 24 units
-                                "window": 210_855_936}    # r2_kernels_full_24units_ncu.txt: k_splat_window, 24 units: 67.8 MB read + 143.0 MB written
+                                "window": 209_976_832}    # r2_kernels_full_24units_ncu.txt: k_splat_window, 24 units: 67.8 MB read + 142.2 MB written
 # DRAM bytes of one whole step from the ncu launch list / full captures of the timed schedule (profiles/), per mode
 NCU_DRAM_BYTES_PER_STEP = {"atomic": 3_160_000_000,      # r1 launch list
-                           "window": 5_206_000_000}      # profiles/r2_launches_summary.txt: 0.219 GB read + 4.987 GB written (588 launches)
+                           "window": 7_645_000_000}      # profiles/r2_launches_summary.txt: 1.943 GB read + 5.702 GB written (99 launches of 12 units: slabs stream through HBM)
 # bytes each kernel itself must move per unit pixel (its own inputs + outputs, intermediates included)
 OWN_BYTES_PER_PX = {"window": {"prepass": 16.0, "splat": 44.0, "normalise": 40.0},       # K1: depth in, flow + z' out; K2: flow, z', RGB in, >= 1 slab cell out; K3: >= 1 slab cell in, 20 B out
                     "atomic": {"prepass": 4.0, "splat": 24.0, "normalise": 40.0}}

@@ -12,5 +12,5 @@ python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; tail -1 
 export TCW_NO_GRAPH=1
 B="python scripts/ncu_target.py 392 3 window 0"
 timeout 300 $B > $O/plain.log 2>&1 && \
-timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -s 1176 -c 588 --csv --log-file $O/launches.csv $B > $O/ncu1.log 2>&1
+timeout 900 ncu --metrics gpu__time_duration.sum,dram__bytes_read.sum,dram__bytes_write.sum --clock-control none -s 198 -c 99 --csv --log-file $O/launches.csv $B > $O/ncu1.log 2>&1
 tail -2 $O/plain.log; ls -la $O
