@@ -522,7 +522,7 @@ def run_ours(args):
         ids = balanced_units(n_all, N_FRAMES, world, rank)
         order = torch.cat([balanced_units(n_all, N_FRAMES, world, r) for r in range(world)])      # unit held at each gathered position
         nl = ids.numel()
-        assert all(balanced_units(n_all, N_FRAMES, world, r).numel() == nl for r in range(world))
+        equal_shards = all(balanced_units(n_all, N_FRAMES, world, r).numel() == nl for r in range(world))      # true for N = 2, 4, 8
         needed, lsrc = sources_of(ssrc, ids)                          # a rank uploads only the source frames its units read
         sf_d, sd_d = sf[needed].contiguous().to(dev), sd[needed].contiguous().to(dev)
         sM_d, ss_d, ids_d = sM[ids].contiguous().to(dev), lsrc.to(dev), ids.to(dev)
@@ -560,7 +560,7 @@ def run_ours(args):
         def nccl_step():
             warp_into(p_col, p_msk, True)
             gathered[0] = gather_packed(packed, n_all, H, W, dst=0)
-        ms_nccl = timed(nccl_step, ksteps)
+        ms_nccl = timed(nccl_step, ksteps) if equal_shards else None      # the single packed gather needs equal shards
         ms_peer = timed(lambda: warp_into(peer.colour, peer.mask, True, scatter=True), ksteps)
         # the assembled clip on rank 0 must equal what one GPU computes for the whole clip, bit for bit (fixed summation order)
         same = None
@@ -568,13 +568,14 @@ def run_ours(args):
             pick = torch.tensor([0, n_all // 2 - 1, n_all // 2, n_all - 1])
             ref_c, ref_m, _, _ = warper.forward_warp_matrices(sf.to(dev), sd.to(dev), sM[pick].to(dev), src_index=ssrc[pick].to(dev),
                                                               per_frame_max=True, check_range=flag, mask_u8=True)
-            parts = unpack_gathered(gathered[0], n_all, H, W)
-            where = torch.empty(n_all, dtype=torch.int64)
-            where[order] = torch.arange(n_all)                       # gathered position of every unit (rank-major blocks)
-            g_col = torch.cat([p_[0] for p_ in parts])[where[pick].to(dev)]
-            same = bool(torch.equal(peer.colour[pick.to(dev)], ref_c) and torch.equal(peer.mask[pick.to(dev)], ref_m)
-                        and torch.equal(g_col, ref_c))
-        wire = 13 * (n_all - n_all // world) * H * W
+            same = bool(torch.equal(peer.colour[pick.to(dev)], ref_c) and torch.equal(peer.mask[pick.to(dev)], ref_m))
+            if ms_nccl is not None:
+                parts = unpack_gathered(gathered[0], n_all, H, W)
+                where = torch.empty(n_all, dtype=torch.int64)
+                where[order] = torch.arange(n_all)                   # gathered position of every unit (rank-major blocks)
+                g_col = torch.cat([p_[0] for p_ in parts])[where[pick].to(dev)]
+                same = same and bool(torch.equal(g_col, ref_c))
+        wire = 13 * (n_all - balanced_units(n_all, N_FRAMES, world, 0).numel()) * H * W
         px_all = n_all * H * W
         strong = {"value": px_all / (ms_strong * 1e-3) / 1e6, "unit": "Mpix/s", "ms": ms_strong, "units_per_rank": nl,
                   "what": "config 2's 392 units of ONE clip sharded over the ranks (a frame block of every trajectory per rank: "
@@ -585,10 +586,10 @@ def run_ours(args):
                        "how": "fused: the gather kernel of every rank stores colour f32 + mask u8 (13 B/px) of each of its units straight "
                               "into that unit's slot of rank 0's buffer (tcw_forward_warp_scatter over a CUDA IPC peer mapping, NVLink / "
                               "NVSwitch); the step ends when all ranks' kernels have finished",
-                       "nccl_single_gather": {"value": px_all / (ms_nccl * 1e-3) / 1e6, "ms": ms_nccl,
-                                              "ingress_GBps": wire / (ms_nccl * 1e-3) / 1e9,
-                                              "how": "warp into a per-rank packed buffer, then ONE dist.gather of 13 B/px (rank-major blocks: "
-                                                     "the clip order still needs a permutation on rank 0, not timed)"},
+                       "nccl_single_gather": None if ms_nccl is None else {
+                           "value": px_all / (ms_nccl * 1e-3) / 1e6, "ms": ms_nccl, "ingress_GBps": wire / (ms_nccl * 1e-3) / 1e9,
+                           "how": "warp into a per-rank packed buffer, then ONE dist.gather of 13 B/px (rank-major blocks: "
+                                  "the clip order still needs a permutation on rank 0, not timed)"},
                        "assembled_equals_single_gpu_bits": same}
         if rank != 0:
             peer.close()          # unmap before the owner frees
