@@ -355,6 +355,7 @@ static void window_plan(const tcw_ctx* ctx, int n_units, size_t hw, int* lanes, 
         g2 = n_units / (NL * 8);
         if (g2 < 2) g2 = 2;
         if (g2 > cap) g2 = cap;
+        if (g2 > 4096) g2 = 4096;                     // (a launch's grid.y)
     }
     const int per_lane = (n_units + NL - 1) / NL;
     if (g2 > per_lane) g2 = per_lane;
