@@ -342,8 +342,9 @@ static void lanes_plan(const tcw_ctx* ctx, int n_units, size_t hw, size_t bytes_
 }
 // The window path's schedule shape (profiles/r2_schedule_sweep.txt, second table): what pays is full launches and enough
 // rounds per lane to hide the tails, not L2 residency of the slabs -- 392 units at 384x672: 4 x 2 4.58 ms, 4 x 12 3.70, plateau
-// 3.65 - 3.70 from 12 units per launch on; 196 units: 4 x 7 1.82 (4 x 2 2.10); 98 and 49 units: 4 x 2..3 is the optimum.
-// Rule: four lanes, about eight rounds per lane, at least two units per launch, at most ~3.7 Mpixel per launch (beyond that a
+// 3.65 - 3.70 from 12 units per launch on; 196 units: 4 x 7 1.82 (4 x 2 2.10); 98 and 49 units: 4 x 4 (the expensive orbit presets
+// gain 27 - 36 % over 4 x 2, the cheapest one loses 3 %).
+// Rule: four lanes, about eight rounds per lane, at least four units per launch, at most ~3.7 Mpixel per launch (beyond that a
 // launch is many waves anyway: one 1080p unit is eight 384x672 units' worth of CTAs).
 static void window_plan(const tcw_ctx* ctx, int n_units, size_t hw, int* lanes, int* chunk) {
     int NL = ctx->lanes > 0 ? ctx->lanes : 4;
@@ -353,7 +354,7 @@ static void window_plan(const tcw_ctx* ctx, int n_units, size_t hw, int* lanes, 
     if (g2 <= 0) {
         const int cap = (int)(3700000 / hw) > 1 ? (int)(3700000 / hw) : 1;
         g2 = n_units / (NL * 8);
-        if (g2 < 2) g2 = 2;
+        if (g2 < 4) g2 = 4;                           // (whole 49-unit presets: 4 x 4 0.47 / 0.54 / 0.62 ms, 4 x 2 0.45 / 0.69 / 0.84)
         if (g2 > cap) g2 = cap;
         if (g2 > 4096) g2 = 4096;                     // (a launch's grid.y)
     }
