@@ -94,3 +94,29 @@ def test_workload_generators_are_deterministic():
     assert ext.shape == (16, 4, 4) and ks.shape == (16, 3, 3)
     R = ext[:, :3, :3]
     assert torch.allclose(R @ R.transpose(1, 2), torch.eye(3).expand(16, 3, 3), atol=1e-5)
+
+
+def test_memoised_inverses_are_the_same_torch_results():
+    """prepare_matrices caches the inverses of repeated small matrices (the reference's per-frame loop, demo.py:77-90): the cached
+    result must be the tensor torch.linalg.inv returns for that input, batched calls bypass the cache, and the cache stays bounded."""
+    import torch
+    from trajectorycrafter_b200 import matrices
+    g = torch.Generator().manual_seed(4)
+    matrices._INV_CACHE.clear()
+    K = torch.tensor([[500.0, 0, 336.0], [0, 500.0, 192.0], [0, 0, 1]])[None]
+    for i in range(5):
+        T1 = torch.eye(4)[None] + 0.1 * torch.rand((1, 4, 4), generator=g)
+        T2 = torch.eye(4)[None] + 0.1 * torch.rand((1, 4, 4), generator=g)
+        for _ in range(2):                                   # second round: served from the cache
+            M = matrices.prepare_matrices(T1, T2, K, None)
+            assert torch.equal(M[:, 9:21], torch.bmm(T2, torch.linalg.inv(T1))[:, :3].reshape(1, 12))
+            assert torch.equal(M[:, 0:9], torch.linalg.inv(K).reshape(1, 9))
+    assert len(matrices._INV_CACHE) == 6                     # five source poses + one intrinsic matrix
+    Tb = torch.eye(4).repeat(12, 1, 1) + 0.1 * torch.rand((12, 4, 4), generator=g)
+    before = len(matrices._INV_CACHE)
+    Mb = matrices.prepare_matrices(Tb, Tb.flip(0), K.repeat(12, 1, 1))
+    assert len(matrices._INV_CACHE) == before                # more than 8 matrices: one LAPACK call, no hashing
+    assert torch.equal(Mb[3:4], matrices.prepare_matrices(Tb[3:4], Tb.flip(0)[3:4], K))      # batched == one by one
+    for i in range(matrices._INV_CACHE_MAX + 10):
+        matrices._inv_cached(torch.eye(3)[None] * (i + 2))
+    assert len(matrices._INV_CACHE) <= matrices._INV_CACHE_MAX
