@@ -334,3 +334,35 @@ def test_twice_batched_call(warper):
     assert mism <= 2 and err <= 2e-5
     valid = (gm > 0) & (tm > 0)
     assert (np.abs(gd - td)[valid] <= 2e-5 * np.abs(td[valid])).all()
+
+
+@pytest.mark.gpu
+def test_infinite_depth_pixels_are_dropped():
+    """Non-finite depth (ADVICE, round 1).  A pixel with depth = +inf projects to NaN coordinates: it adds nothing, its neighbours
+    are untouched, its flow12 is NaN, and no NaN reaches colour / mask / depth -- the oracle's behaviour, pinned here for the CUDA
+    path.  (Documented deviation, DESIGN.md section 1: in the reference such a pixel's z' = inf - inf = NaN poisons
+    log_depth.max(), models/utils.py:492, and with it every weight of the call: its whole frame comes out invalid.  The
+    reference's own depth stage clips to [1e-4, 1e4], models/infer.py:90, so its pipelines never produce one.)
+    A huge finite depth (1e30) behaves like the reference in both."""
+    import torch
+    from trajectorycrafter_b200 import Warper, prepare_matrices
+    from trajectorycrafter_b200.workloads import orbit_units, synthetic_clip
+    h, w = 72, 100
+    frames, depths = synthetic_clip(2, h, w, seed=2)
+    T1, T2, K, src = orbit_units(depths, h, w, presets=[(5, 25), (-10, -60)])
+    depths = depths.clone()
+    depths[0, 0, 5, 7] = float("inf"); depths[0, 0, 20, 30] = float("inf"); depths[1, 0, 21, 31] = 1e30; depths[1, 0, 60, 90] = float("inf")
+    M = prepare_matrices(T1, T2, K)
+    wp = Warper(device="cuda:0")
+    for mode in ("window", "atomic"):
+        got = [npy(t) for t in wp.forward_warp_matrices(frames, depths, M, src_index=src, accumulation=mode)]
+        ref = oracle.forward_warp(frames, None, depths, M, src_index=src.numpy(), per_unit_max=True)
+        assert not np.isnan(got[0]).any() and not np.isnan(got[1]).any() and not np.isnan(got[2]).any(), mode
+        assert np.array_equal(got[1], ref[1]), f"{mode}: validity mask"
+        assert np.array_equal(np.isnan(got[3]), np.isnan(ref[3])) and np.isnan(ref[3]).sum() >= 6, f"{mode}: NaN flow exactly where the oracle has it"
+        fin = ~np.isnan(ref[3])
+        assert np.array_equal(got[3][fin], ref[3][fin]), f"{mode}: flow12 elsewhere bit-exact"
+        count = oracle.contrib_count(np.nan_to_num(ref[3], nan=1e6))
+        assert_colour_close(got[0], ref[0], count=count, what=f"inf depth {mode}")
+        assert_depth_close(got[2], ref[2], ref[1], count=count, what=f"inf depth {mode}")
+        assert float(ref[1].mean()) > 0.5
