@@ -109,7 +109,9 @@ ORC_EXPORT int orc_splat(const float* frame, const float* mask1, const float* de
     const size_t hw = (size_t)h * w;
     const int ph = h + 2, pw = w + 2;
     const size_t phw = (size_t)ph * pw;
-    /* log_depth1 = log(1 + clamp(depth, 0, 1000)); global max   :490-492 */
+    /* log_depth1 = log(1 + clamp(depth, 0, 1000)); global max   :490-492
+     * DEVIATION (documented): torch's max() propagates a NaN (a non-finite input depth whose z' is
+     * inf - inf), which invalidates the reference's whole frame; `ld > L` below ignores it and only that pixel is dropped. */
     float L = -INFINITY;
     for (size_t i = 0; i < (size_t)b * hw; ++i) {
         float ld = logf(1.0f + clampf(depth[i], 0.0f, 1000.0f));
